@@ -1,0 +1,366 @@
+#!/usr/bin/env python3
+"""bench.py — converted frames/sec of the fused pre-encode stage on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A *step* is one pass of the hot path over one batch of synthetic input: S
+independent 3840x2160 desktop sessions (BASELINE.json configs[1], the largest
+single-GPU config the metric is quoted on) converted BGRx→NV12 with damage
+maps by ONE kernel launch (sk_batch_submit).  Each session keeps two captured
+frames resident in HBM and alternates between them, so every step reads
+S*33.2 MB of BGRx + S*12.4 MB of previous output and writes S*12.4 MB: the
+working set (≈0.9 GB at S=16) is far larger than the 126 MB L2.
+
+Lines printed (one JSON object, rank 0 only):
+  value     frames/s with inputs already in HBM (device-event timed, max over ranks)
+  e2e       same metric through the C ABI with HOST buffers: pinned staging → H2D →
+            kernel → D2H of the NV12 frame + map, every step, wall-clock between syncs
+  roofline  algorithmic bytes per launch / CUDA-event kernel time vs MEASURED_PEAKS.json
+  cpu_baseline  the C oracle (restatement of videoconvert, "port") on the host cores
+
+`--impl reference` times that CPU path alone on the same workload (GStreamer
+itself cannot be installed here).
+Under torchrun (N>1) sessions are sharded S per GPU with no data-path
+collective; torch.distributed (gloo) is used only for the barrier and the
+max-over-ranks of the timing.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 3840, 2160
+WORKLOAD = "3840x2160 BGRx -> NV12 fused convert + damage map on 1xB200"
+METRIC = "converted frames/sec @4K per GPU (fused BGRx->NV12 + 16x16 damage map)"
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------- CPU arm
+def make_inputs(n_sessions: int, rank: int):
+    """Two captured frames per session: desktop content, then 5 % of its macroblocks changed."""
+    from selkies_gstreamer_b200 import synth
+    base = synth.desktop(W, H, seed=42 + rank)
+    out = []
+    for i in range(n_sessions):
+        a = np.roll(base, shift=(37 * i, 101 * i), axis=(0, 1))
+        b = synth.mutate(a, 0.05, seed=1000 * rank + i, aligned=False)
+        out.append((a, b))
+    return out
+
+
+def cpu_pass(frames, prevs, threads):
+    """One step on the host: convert + damage for every session. Returns new outputs."""
+    from oracle import cpu_oracle as o
+    outs = []
+    for f, p in zip(frames, prevs):
+        cur = o.convert(f, out_fmt=o.OUT_NV12, matrix=o.MATRIX_BT709, chroma_site=o.SITE_H_COSITED, n_threads=threads)
+        o.damage(W, H, o.OUT_NV12, cur, p)
+        outs.append(cur)
+    return outs
+
+
+def cpu_baseline(budget_s: float = 12.0):
+    """Bounded sample of the same workload on this box's host cores (C oracle, 'port')."""
+    from oracle import cpu_oracle as o
+    o.build()
+    threads = len(os.sched_getaffinity(0))
+    pair = make_inputs(1, 0)[0]
+    prev = cpu_pass([pair[0]], [None], threads)
+    n, t0 = 0, time.perf_counter()
+    while True:
+        prev = cpu_pass([pair[n & 1]], prev, threads)
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or n >= 2000:
+            break
+    return {"value": n / dt, "unit": "frames/s", "cores": threads, "kind": "port",
+            "sample": f"{n} 4K frames, convert+damage, C oracle with {threads} row-band threads, {dt:.1f} s"}
+
+
+def run_reference(args, rank, world):
+    """--impl reference: the CPU path on the host cores, same workload/metric."""
+    if rank != 0:
+        return
+    from oracle import cpu_oracle as o
+    o.build()
+    threads = len(os.sched_getaffinity(0))
+    s = min(args.sessions, 4)        # bounded sample of the S-session batch
+    inputs = make_inputs(s, 0)
+    prevs = cpu_pass([p[0] for p in inputs], [None] * s, threads)
+    for k in range(args.warmup):
+        prevs = cpu_pass([p[(k + 1) & 1] for p in inputs], prevs, threads)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        prevs = cpu_pass([p[(k + args.warmup + 1) & 1] for p in inputs], prevs, threads)
+    dt = time.perf_counter() - t0
+    fps = s * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sessions_per_step": s,
+                   "note": "CPU restatement of GStreamer videoconvert (+damage) — GStreamer itself is not installable here"},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": threads, "kind": "port",
+                         "sample": f"{s} 4K frames per step x {args.steps} steps, {threads} threads"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_b200(args, rank, world, local_rank, dist):
+    import selkies_gstreamer_b200 as sk
+    from selkies_gstreamer_b200 import _abi, synth
+
+    lib = _abi.load()
+    if lib.sk_device_count() <= local_rank:
+        raise SystemExit(f"rank {rank}: CUDA device {local_rank} not available — the product path has no fallback")
+    if args.variant is not None:
+        lib.sk_set_kernel_variant(args.variant)
+    S = args.sessions
+    inputs = make_inputs(S, rank)
+
+    # ---- device-resident arm: S sessions, one launch per step
+    sess = [sk.PreencodeSession(W, H, out_format="NV12", colorimetry="bt709", chroma_site="mpeg2",
+                                device_id=local_rank, n_inflight=2, host_output=False, timing=(i == 0))
+            for i in range(S)]
+    for s, (a, b) in zip(sess, inputs):
+        s.upload(0, a); s.wait(s.submit(0))
+        s.upload(1, b); s.wait(s.submit(1))
+    ptrs = [[s.device_input(k)[0] for s in sess] for k in (0, 1)]
+    stride = sess[0].device_input(0)[1]
+    leader = sess[0]
+    fid = 1000
+
+    def step(k, wait_prev=True):
+        nonlocal fid
+        sk.batch_submit(sess, ptrs[k & 1], stride, fid)
+        if wait_prev and fid > 1000:
+            for s in sess:
+                s.wait(fid - 1)
+        fid += 1
+
+    def sync_all():
+        for s in sess:
+            s.wait(fid - 1)
+
+    for k in range(args.warmup):
+        step(k)
+    sync_all()
+    if dist:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = sk.launch_count()
+    kernel_us = []
+    leader.marker(0)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(k + args.warmup)
+        if k > 0:
+            kernel_us.append(leader.last_kernel_us())
+    leader.marker(1)
+    sync_all()
+    wall = time.perf_counter() - t0
+    kernel_us.append(leader.last_kernel_us())
+    dev_us = leader.marker_elapsed_us()
+    launches = sk.launch_count() - launches0
+    clocks = sampler.stop()
+    # last result sanity: ~5 % of blocks damaged, never 0 and never all
+    r = sess[1].wait(fid - 1)
+    nblk = r.damage_map.size
+    assert 0 < r.damaged_count < nblk, (r.damaged_count, nblk)
+
+    elapsed = max(dev_us * 1e-6, 1e-9)
+    if dist:
+        import torch
+        t = torch.tensor([elapsed, wall], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed, wall = float(t[0]), float(t[1])
+    frames_total = S * args.steps * world
+    value = frames_total / elapsed
+
+    # ---- end-to-end arm: host staging → H2D → kernel → D2H frame + map
+    for s in sess[4:]:
+        s.close()
+    for s in sess[:4]:
+        s.close()
+    Se = min(args.e2e_sessions, S)
+    esess = [sk.PreencodeSession(W, H, out_format="NV12", colorimetry="bt709", chroma_site="mpeg2",
+                                 device_id=local_rank, n_inflight=2, host_output=True) for _ in range(Se)]
+    for s, (a, b) in zip(esess, inputs):
+        s.upload(0, a)
+        s.upload(1, b)
+    esteps = max(3, min(args.steps, args.e2e_steps))
+
+    def estep(k):
+        ids = [s.submit(k & 1) for s in esess]
+        out = 0
+        for s, i in zip(esess, ids):
+            out += s.wait(i).damaged_count
+        return out
+
+    for k in range(3):
+        estep(k)
+    if dist:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for k in range(esteps):
+        estep(k + 3)
+    e2e_t = time.perf_counter() - t0
+    if dist:
+        import torch
+        t = torch.tensor([e2e_t], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_t = float(t[0])
+    e2e_fps = Se * esteps * world / e2e_t
+    frame_bytes = esess[0].frame_bytes
+    meta_bytes = ((r.damage_map.size + 3) // 4) * 4 + 4
+    for s in esess:
+        s.close()
+
+    if rank != 0:
+        return
+    peak, peak_src = measured_peak()
+    bytes_per_frame = synth.algorithmic_bytes(W, H, W, H, damage=True)
+    k_us = statistics.mean(kernel_us)
+    achieved = bytes_per_frame * S / (k_us * 1e-6) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    cpu = cpu_baseline() if not args.no_cpu_baseline else None
+    line = {
+        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": elapsed / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sessions_per_gpu": S, "step": "one sk_batch_submit launch over all sessions",
+                   "matrix": "bt709", "chroma_site": "h-cosited", "l2": "inputs larger than L2 "
+                   f"({S}x(33.2+12.4+12.4) MB per step, two resident frames per session alternated)",
+                   "kernel_variant": args.variant if args.variant is not None else 0},
+        "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": Se * 4 * W * H,
+                "d2h_bytes_per_step": Se * (frame_bytes + meta_bytes), "sessions": Se, "steps": esteps,
+                "timing": "wall clock between host syncs, max over ranks"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src, "frac_of_8TBs_nominal": achieved / 8000.0,
+                     "kernel_us_per_launch": k_us, "algorithmic_bytes_per_launch": bytes_per_frame * S},
+        "wall_s_timed_region": wall,
+    }
+    if cpu:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--sessions", type=int, default=16, help="4K sessions per GPU (one launch per step)")
+    ap.add_argument("--e2e-sessions", type=int, default=4)
+    ap.add_argument("--e2e-steps", type=int, default=40)
+    ap.add_argument("--variant", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        if args.steps > 20:
+            args.steps = 20          # bounded: each step is already seconds of CPU work
+        run_reference(args, rank, world)
+        return
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist_mod.init_process_group(backend="gloo", rank=rank, world_size=world)
+        dist = dist_mod
+    try:
+        run_b200(args, rank, world, local_rank, dist)
+    finally:
+        if dist:
+            dist.barrier()
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

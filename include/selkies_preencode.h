@@ -1,0 +1,185 @@
+/*
+ * selkies_preencode.h — C ABI of the B200 pre-encode stage.
+ *
+ * One shared library (libselkies_preencode.so, hand-written sm_100a CUDA + a
+ * small C++ runtime) replaces the elements the reference instantiates between
+ * ximagesrc and the video encoder:
+ *
+ *   videoconvert (+ capsfilter NV12 / I420)   src/selkies/legacy/gstwebrtc_app.py:611-617,
+ *                                             :643-649, :669-675, :686-692, :725-731, :742-748, :767-773
+ *   cudaupload + cudaconvert (+ NV12 caps)    src/selkies/legacy/gstwebrtc_app.py:263-284, :370-380, :427-437
+ *   (would-be) videoscale method=bilinear     no call site; resolution comes from
+ *                                             src/selkies/legacy/resize.py:15-29
+ *
+ * It is bound from Python with ctypes (selkies_gstreamer_b200/_abi.py); the
+ * GstBase.BaseTransform element in selkies_gstreamer_b200/gst_element.py is the
+ * drop-in for the factories above.  Plain C types only; no exception crosses;
+ * every function returns an int status (0 = SK_OK, negative = error) unless
+ * stated otherwise.  There is no CPU fallback: without a CUDA device every
+ * entry point that touches a frame fails with SK_ERR_CUDA.
+ *
+ * Ownership: the library owns all device memory, pinned staging, streams and
+ * events of a session.  Callers own their frame buffers and only borrow the
+ * pointers returned in sk_result until the slot / ring entry is reused.
+ * Threading: one producer thread per session (GStreamer's streaming thread);
+ * different sessions are independent.
+ */
+#ifndef SELKIES_PREENCODE_H
+#define SELKIES_PREENCODE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SK_ABI_VERSION 1
+
+/* status codes */
+enum {
+    SK_OK = 0,
+    SK_ERR_ARG = -1,          /* bad pointer / enum / geometry (odd or out-of-range size)      */
+    SK_ERR_CUDA = -2,         /* CUDA runtime error, incl. "no device"; see sk_last_error()    */
+    SK_ERR_ALIGN = -3,        /* device input pointer / stride not 16-byte aligned             */
+    SK_ERR_STATE = -4,        /* slot busy, unknown frame id, session mismatch in a batch      */
+    SK_ERR_UNSUPPORTED = -5,  /* e.g. up-scaling (reference never enlarges before the encoder) */
+    SK_ERR_NOMEM = -6
+};
+
+/* sink caps formats that ximagesrc can negotiate (gstwebrtc_app.py:210-255; docs/component.md:336) */
+enum { SK_IN_BGRX = 0, SK_IN_RGBX = 1, SK_IN_BGRA = 0, SK_IN_RGBA = 1 };
+/* src caps formats forced by the capsfilter after the stage (gstwebrtc_app.py:615 NV12, :647 I420) */
+enum { SK_OUT_NV12 = 0, SK_OUT_I420 = 1 };
+/* colorimetry of the src caps; GStreamer's default by output height is applied by the Python host */
+enum { SK_MATRIX_BT601 = 0, SK_MATRIX_BT709 = 1, SK_MATRIX_BT2020 = 2 };
+/* chroma-site of the src caps */
+enum { SK_SITE_NONE = 0, SK_SITE_H_COSITED = 1 };
+/* videoscale "method": only bilinear (2-tap) is required */
+enum { SK_SCALE_BILINEAR = 1 };
+/* resampler restatement variant ("scale") */
+enum { SK_SCALE_VARIANT_GST_LQ = 0, SK_SCALE_VARIANT_PLAIN_LQ = 1 };
+
+/* sk_config.flags */
+enum {
+    SK_FLAG_NO_DAMAGE   = 1 << 0,  /* convert-only: no previous-frame read, no map                   */
+    SK_FLAG_HOST_OUTPUT = 1 << 1,  /* copy the converted frame back to pinned host memory each frame */
+    SK_FLAG_TIMING      = 1 << 2   /* record CUDA events; sk_result.*_us are filled                  */
+};
+
+typedef struct sk_session sk_session;
+
+/*
+ * Replaces: the GObject properties + negotiated caps of the stage
+ * (cuda-device-id gstwebrtc_app.py:264-272; n-threads/qos :612-613; caps :614-617).
+ */
+typedef struct sk_config {
+    uint32_t struct_size;     /* = sizeof(sk_config); ABI versioning                              */
+    int32_t  device_id;       /* cuda-device-id; -1 = device 0                                     */
+    int32_t  in_width, in_height;
+    int32_t  in_stride;       /* bytes per captured row; 0 = 4*in_width                            */
+    int32_t  in_format;       /* SK_IN_*                                                           */
+    int32_t  out_width, out_height;   /* 0 = same as input                                         */
+    int32_t  out_format;      /* SK_OUT_*                                                          */
+    int32_t  matrix;          /* SK_MATRIX_*                                                       */
+    int32_t  chroma_site;     /* SK_SITE_*                                                         */
+    int32_t  scale_method;    /* SK_SCALE_BILINEAR (ignored when sizes are equal)                  */
+    int32_t  scale_variant;   /* SK_SCALE_VARIANT_*                                                */
+    int32_t  n_inflight;      /* staging slots and output ring depth, 2..8 (0 = 2)                 */
+    uint32_t flags;           /* SK_FLAG_*                                                         */
+} sk_config;
+
+/* What one converted frame looks like to the caller (GstVideoInfo default layout). */
+typedef struct sk_result {
+    uint64_t frame_id;
+    const uint8_t *dev_frame;     /* packed output frame in HBM                                   */
+    const uint8_t *host_frame;    /* pinned copy when SK_FLAG_HOST_OUTPUT, else NULL              */
+    size_t   frame_bytes;
+    size_t   plane_offset[3];     /* Y, U (or interleaved UV), V (0 for NV12)                     */
+    int32_t  plane_stride[3];
+    const uint8_t *host_damage_map; /* pinned, uint8[mb_h][mb_w], 1 = damaged; NULL if NO_DAMAGE  */
+    const uint8_t *dev_damage_map;
+    int32_t  mb_w, mb_h;
+    uint32_t damaged_count;       /* exact sum of the map                                         */
+    float    h2d_us, kernel_us, d2h_us;   /* only with SK_FLAG_TIMING                             */
+} sk_result;
+
+/* Replaces: Gst.ElementFactory.make("videoconvert"/"cudaconvert") + set_caps
+ * (gstwebrtc_app.py:611, :270). Allocates everything the session will ever use. */
+int sk_session_create(const sk_config *cfg, sk_session **out);
+
+/* Replaces: element finalize at pipeline teardown (gstwebrtc_app.py:1727-1742). */
+int sk_session_destroy(sk_session *s);
+
+/* Pinned, library-owned staging for slot in [0, n_inflight): the capture side
+ * writes the BGRx frame here (replaces cudaupload's GstBuffer input,
+ * gstwebrtc_app.py:263-265).  Rows are in_stride bytes apart. */
+int sk_get_input_staging(sk_session *s, int slot, void **host_ptr, size_t *bytes);
+
+/* Device-side copy of staging slot `slot` (valid after an sk_submit of that
+ * slot has completed): lets a caller re-submit a resident frame with
+ * sk_submit_device / sk_batch_submit without another upload. */
+int sk_get_device_input(sk_session *s, int slot, void **dptr, size_t *stride);
+
+/* Copy a caller-owned (pageable or pinned) frame into staging slot `slot`
+ * on the calling thread (replaces the GstBuffer map + upload of cudaupload). */
+int sk_upload(sk_session *s, int slot, const void *src, size_t src_stride);
+
+/* Asynchronous: H2D of staging slot on the copy stream, then the fused
+ * convert[+scale]+damage kernel on the compute stream, then D2H of the map
+ * (and of the frame with SK_FLAG_HOST_OUTPUT).  Replaces one
+ * GstBaseTransform::transform call of the stage (upstream), as driven by the
+ * pipeline assembled at gstwebrtc_app.py:941-994. */
+int sk_submit(sk_session *s, int slot, uint64_t frame_id);
+
+/* Same, for a frame that is already in HBM (video/x-raw(memory:CUDAMemory)
+ * input, gstwebrtc_app.py:281-284, and the device-resident benchmark).
+ * dptr and stride must be 16-byte aligned. */
+int sk_submit_device(sk_session *s, const void *dptr, size_t stride, uint64_t frame_id);
+
+/* Block until frame_id is complete and describe it. */
+int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out);
+
+/* Next frame is treated as having no predecessor: map = all ones.  Replaces the
+ * renegotiation after a resize (src/selkies/legacy/webrtc_input.py:672-678 →
+ * resize.py:75-117) or a keyframe request. */
+int sk_reset_history(sk_session *s);
+
+/* One launch over n sessions of identical configuration on the same device
+ * (throughput mode: independent desktop sessions, gstwebrtc_app.py:264-272
+ * pins each to a GPU).  dptrs[i] is session i's frame in HBM (stride as in
+ * sk_submit_device); all get frame_id.  Completion via sk_wait on each. */
+int sk_batch_submit(sk_session **sessions, int n, const void *const *dptrs,
+                    size_t stride, uint64_t frame_id);
+
+/* Device-side time of the last `sk_batch_submit`/`sk_submit*` kernel launch on
+ * this session in microseconds (needs SK_FLAG_TIMING), for roofline accounting. */
+int sk_last_kernel_us(sk_session *s, float *us);
+
+/* Measurement helpers: record a CUDA event (which = 0 start, 1 stop) on the
+ * session's compute stream, and read the device time between them.  Used by
+ * bench.py to time K steps on the stream the kernels run on.  (The reference
+ * has no timing hooks for this stage; its only knob is GST_TRACERS.) */
+int sk_marker_record(sk_session *s, int which);
+int sk_marker_elapsed_us(sk_session *s, float *us);
+
+/* Number of kernel launches issued by this library in this process so far. */
+uint64_t sk_launch_count(void);
+
+/* Human-readable description of the last error on this session (or of the
+ * last failed sk_session_create when s == NULL).  Owned by the library. */
+const char *sk_last_error(sk_session *s);
+
+/* SK_ABI_VERSION of the loaded library. */
+int sk_version(void);
+
+/* Number of CUDA devices visible (0 on a CPU-only host; never fails). */
+int sk_device_count(void);
+
+/* Kernel-variant selector for tuning runs (0 = library default); process-wide. */
+int sk_set_kernel_variant(int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SELKIES_PREENCODE_H */

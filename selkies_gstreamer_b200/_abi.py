@@ -1,0 +1,133 @@
+"""ctypes declarations for libselkies_preencode.so (include/selkies_preencode.h).
+
+No PyTorch, no CPU fallback: if the library is missing or has no CUDA device to
+run on, callers get an exception, never a silently different code path.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libselkies_preencode.so")
+CSRC = os.path.join(_PKG, "csrc")
+
+SK_OK = 0
+SK_ERR_ARG, SK_ERR_CUDA, SK_ERR_ALIGN, SK_ERR_STATE, SK_ERR_UNSUPPORTED, SK_ERR_NOMEM = -1, -2, -3, -4, -5, -6
+SK_IN_BGRX, SK_IN_RGBX = 0, 1
+SK_OUT_NV12, SK_OUT_I420 = 0, 1
+SK_MATRIX_BT601, SK_MATRIX_BT709, SK_MATRIX_BT2020 = 0, 1, 2
+SK_SITE_NONE, SK_SITE_H_COSITED = 0, 1
+SK_SCALE_BILINEAR = 1
+SK_SCALE_VARIANT_GST_LQ, SK_SCALE_VARIANT_PLAIN_LQ = 0, 1
+SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING = 1, 2, 4
+SK_MAX_BATCH = 32
+SK_ABI_VERSION = 1
+
+# Every symbol include/selkies_preencode.h declares (tests check the .so exports all of them).
+EXPORTS = (
+    "sk_session_create", "sk_session_destroy", "sk_get_input_staging", "sk_get_device_input",
+    "sk_upload", "sk_submit", "sk_submit_device", "sk_wait", "sk_reset_history",
+    "sk_batch_submit", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
+    "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
+)
+
+
+class SkConfig(ctypes.Structure):
+    _fields_ = [
+        ("struct_size", ctypes.c_uint32),
+        ("device_id", ctypes.c_int32),
+        ("in_width", ctypes.c_int32), ("in_height", ctypes.c_int32),
+        ("in_stride", ctypes.c_int32),
+        ("in_format", ctypes.c_int32),
+        ("out_width", ctypes.c_int32), ("out_height", ctypes.c_int32),
+        ("out_format", ctypes.c_int32),
+        ("matrix", ctypes.c_int32),
+        ("chroma_site", ctypes.c_int32),
+        ("scale_method", ctypes.c_int32),
+        ("scale_variant", ctypes.c_int32),
+        ("n_inflight", ctypes.c_int32),
+        ("flags", ctypes.c_uint32),
+    ]
+
+
+class SkResult(ctypes.Structure):
+    _fields_ = [
+        ("frame_id", ctypes.c_uint64),
+        ("dev_frame", ctypes.c_void_p),
+        ("host_frame", ctypes.c_void_p),
+        ("frame_bytes", ctypes.c_size_t),
+        ("plane_offset", ctypes.c_size_t * 3),
+        ("plane_stride", ctypes.c_int32 * 3),
+        ("host_damage_map", ctypes.c_void_p),
+        ("dev_damage_map", ctypes.c_void_p),
+        ("mb_w", ctypes.c_int32), ("mb_h", ctypes.c_int32),
+        ("damaged_count", ctypes.c_uint32),
+        ("h2d_us", ctypes.c_float), ("kernel_us", ctypes.c_float), ("d2h_us", ctypes.c_float),
+    ]
+
+
+class PreencodeLibraryError(RuntimeError):
+    """The native library is missing, stale or unusable. There is no fallback."""
+
+
+def build(force: bool = False) -> str:
+    """Compile the library in-tree with nvcc for sm_100a (seconds; works without a GPU)."""
+    srcs = [os.path.join(CSRC, f) for f in ("sk_kernels.cu", "sk_session.cu", "sk_kernels.h")]
+    srcs.append(os.path.join(_PKG, "..", "include", "selkies_preencode.h"))
+    stale = (not os.path.exists(LIB_PATH)
+             or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(s) for s in srcs))
+    if force or stale:
+        subprocess.check_call(["make", "-C", CSRC, "-B"], stdout=subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """dlopen the library and declare every prototype. Raises if it is absent."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise PreencodeLibraryError(
+            f"{LIB_PATH} not found: build it with `make -C {CSRC}` (or __graft_entry__.build()). "
+            "This package has no CPU or PyTorch fallback.")
+    L = ctypes.CDLL(LIB_PATH)
+    vp, vpp = ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)
+    i, u64, sz = ctypes.c_int, ctypes.c_uint64, ctypes.c_size_t
+    fp = ctypes.POINTER(ctypes.c_float)
+    protos = {
+        "sk_session_create": (i, [ctypes.POINTER(SkConfig), vpp]),
+        "sk_session_destroy": (i, [vp]),
+        "sk_get_input_staging": (i, [vp, i, vpp, ctypes.POINTER(sz)]),
+        "sk_get_device_input": (i, [vp, i, vpp, ctypes.POINTER(sz)]),
+        "sk_upload": (i, [vp, i, vp, sz]),
+        "sk_submit": (i, [vp, i, u64]),
+        "sk_submit_device": (i, [vp, vp, sz, u64]),
+        "sk_wait": (i, [vp, u64, ctypes.POINTER(SkResult)]),
+        "sk_reset_history": (i, [vp]),
+        "sk_batch_submit": (i, [vpp, i, vpp, sz, u64]),
+        "sk_last_kernel_us": (i, [vp, fp]),
+        "sk_marker_record": (i, [vp, i]),
+        "sk_marker_elapsed_us": (i, [vp, fp]),
+        "sk_launch_count": (u64, []),
+        "sk_last_error": (ctypes.c_char_p, [vp]),
+        "sk_version": (i, []),
+        "sk_device_count": (i, []),
+        "sk_set_kernel_variant": (i, [i]),
+    }
+    assert set(protos) == set(EXPORTS)
+    for name, (res, args) in protos.items():
+        try:
+            fn = getattr(L, name)
+        except AttributeError as e:
+            raise PreencodeLibraryError(f"{LIB_PATH} does not export {name}; rebuild it") from e
+        fn.restype = res
+        fn.argtypes = args
+    if L.sk_version() != SK_ABI_VERSION:
+        raise PreencodeLibraryError(f"ABI version mismatch: library {L.sk_version()}, binding {SK_ABI_VERSION}")
+    _lib = L
+    return L

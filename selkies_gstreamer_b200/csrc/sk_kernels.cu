@@ -1,0 +1,518 @@
+// sk_kernels.cu — fused pre-encode kernels for sm_100a (B200).
+//
+// One pass per frame replaces what the reference's pipeline runs between
+// ximagesrc and the encoder (src/selkies/legacy/gstwebrtc_app.py:611-617
+// videoconvert → NV12/I420; :263-284 cudaupload+cudaconvert → NV12):
+//
+//   BGRx/RGBx read (128-bit coalesced) → integer 3x4 matrix (dp4a, 8 fractional
+//   bits, no rounding term) → 4:2:0 chroma (h filter with a warp-shuffle halo,
+//   then v average) → Y/UV stores in GstVideoInfo layout → compare against the
+//   previous output frame (kept resident in HBM) → per-16x16 damage flags by
+//   warp ballot + shared-memory OR, damaged count by one atomic per block.
+//
+// HBM-bound integer work: no tensor cores on purpose.  Algorithmic traffic is
+// 4 B/px in + 1.5 B/px out + 1.5 B/px previous frame (+1 B per macroblock).
+#include "sk_kernels.h"
+
+namespace {
+
+constexpr int kThreads = 256;         // 8 warps per CTA
+constexpr uint32_t kFull = 0xffffffffu;
+
+__device__ __forceinline__ uint32_t dp4a_uu(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("dp4a.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t dp4a_us(uint32_t a, uint32_t b, int c)
+{
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return (uint32_t)d;
+}
+
+// ---- loads -----------------------------------------------------------------
+template <int HINT> __device__ __forceinline__ uint4 ld16(const void *p)
+{
+    if (HINT == 1) return __ldcs(reinterpret_cast<const uint4 *>(p));
+    return __ldg(reinterpret_cast<const uint4 *>(p));
+}
+template <int HINT> __device__ __forceinline__ uint2 ld8(const void *p)
+{
+    if (HINT == 1) return __ldcs(reinterpret_cast<const uint2 *>(p));
+    return __ldg(reinterpret_cast<const uint2 *>(p));
+}
+template <int HINT> __device__ __forceinline__ uint32_t ld4(const void *p)
+{
+    if (HINT == 1) return __ldcs(reinterpret_cast<const uint32_t *>(p));
+    return __ldg(reinterpret_cast<const uint32_t *>(p));
+}
+template <int HINT> __device__ __forceinline__ uint32_t ld2(const void *p)
+{
+    if (HINT == 1) return __ldcs(reinterpret_cast<const unsigned short *>(p));
+    return __ldg(reinterpret_cast<const unsigned short *>(p));
+}
+__device__ __forceinline__ uint32_t ld1(const void *p)
+{
+    return __ldg(reinterpret_cast<const unsigned char *>(p));
+}
+
+// nv = number of valid pixels of this quad: 4, 2 or 0 (W is even).
+template <int HINT> __device__ __forceinline__ uint4 load_quad(const uint8_t *p, int nv)
+{
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (nv == 4) {
+        v = ld16<HINT>(p);
+    } else if (nv == 2) {
+        uint2 t = ld8<HINT>(p);
+        v.x = t.x;  v.y = t.y;
+    }
+    return v;
+}
+template <int HINT> __device__ __forceinline__ uint32_t load_word(const uint8_t *p, int nv)
+{
+    if (nv == 4) return ld4<HINT>(p);
+    if (nv == 2) return ld2<HINT>(p);
+    return 0;
+}
+__device__ __forceinline__ void store_word(uint8_t *p, uint32_t w, int nv)
+{
+    if (nv == 4) *reinterpret_cast<uint32_t *>(p) = w;
+    else if (nv == 2) *reinterpret_cast<unsigned short *>(p) = (unsigned short)w;
+}
+
+// ---- arithmetic -------------------------------------------------------------
+// Four pixels → packed Y word and four (U | V<<16) lane pairs.
+__device__ __forceinline__ void matrix_quad(const uint4 &q, const SkGeom &g, uint32_t &yw, uint32_t uv[4])
+{
+    const uint32_t p[4] = {q.x, q.y, q.z, q.w};
+    uint32_t ay[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        ay[i] = dp4a_uu(p[i], g.cy, 4096u);
+        uint32_t au = dp4a_us(p[i], g.cu, 32768);
+        uint32_t av = dp4a_us(p[i], g.cv, 32768);
+        uv[i] = __byte_perm(au, av, 0x7531);   // (au>>8)&0xff | ((av>>8)&0xff)<<16 (sums < 65536)
+    }
+    uint32_t t01 = __byte_perm(ay[0], ay[1], 0x0051);
+    uint32_t t23 = __byte_perm(ay[2], ay[3], 0x0051);
+    yw = __byte_perm(t01, t23, 0x5410);
+}
+
+// Horizontal 4:2:0 filter on 16-bit lanes; x = first pixel of the quad.
+template <int SITE>
+__device__ __forceinline__ void chroma_h(const uint32_t uv[4], uint32_t left, int x, int w,
+                                         uint32_t &h0, uint32_t &h1)
+{
+    if (SITE == 0) {
+        h0 = ((uv[0] + uv[1] + 0x00010001u) >> 1) & 0x00ff00ffu;
+        h1 = ((uv[2] + uv[3] + 0x00010001u) >> 1) & 0x00ff00ffu;
+    } else {
+        const bool closing = w > 2;
+        uint32_t l0 = (x == 0) ? uv[0] : left;                      // [3 1] opening tap
+        uint32_t r0 = (closing && x == w - 2) ? uv[0] : uv[1];      // [1 3] closing tap (partial quad)
+        uint32_t r1 = (closing && x + 2 == w - 2) ? uv[2] : uv[3];  // [1 3] closing tap (full quad)
+        h0 = ((l0 + 2u * uv[0] + r0 + 0x00020002u) >> 2) & 0x00ff00ffu;
+        h1 = ((uv[1] + 2u * uv[2] + r1 + 0x00020002u) >> 2) & 0x00ff00ffu;
+    }
+}
+
+// Vertical average of two filtered rows and byte gather.
+// NV12 → U0 V0 U1 V1 ; I420 → U0 U1 V0 V1 (low half to the U plane, high half to V).
+template <int FMT>
+__device__ __forceinline__ uint32_t chroma_v(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1)
+{
+    uint32_t v0 = (a0 + b0 + 0x00010001u) >> 1;
+    uint32_t v1 = (a1 + b1 + 0x00010001u) >> 1;
+    return __byte_perm(v0, v1, FMT == 0 ? 0x6420 : 0x6240);
+}
+
+// Block-level tail of the damage reduction: one atomic per CTA into the running
+// count, then a wrapping ticket; the last CTA of this frame publishes the total
+// and leaves both scratch words at zero for the next launch.
+__device__ __forceinline__ void finish_count(const SkFrame &f, uint32_t votes)
+{
+    if (votes) atomicAdd(&f.scratch[0], (uint32_t)__popc(votes));
+    __threadfence();
+    const uint32_t nblk = gridDim.x * gridDim.y;
+    uint32_t t = atomicInc(&f.scratch[1], nblk - 1);
+    if (t == nblk - 1) {
+        __threadfence();
+        *f.count_out = atomicExch(&f.scratch[0], 0u);
+    }
+}
+
+// ---- no-scale kernel ----------------------------------------------------------
+// CTA = 8 warps.  A warp covers 128*QX pixels of 2*RP rows; lane l owns the
+// quads at x = bx0 + q*128 + 4*l.  The CTA covers 16*RP rows = RP macroblock
+// rows, so a macroblock is 4 adjacent lanes of 8/RP adjacent warps.
+template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT>
+__global__ void __launch_bounds__(kThreads)
+sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+{
+    constexpr int ROWS = 2 * RP;
+    const SkFrame &f = batch.f[blockIdx.z];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int bx0 = blockIdx.x * (128 * QX);
+    const int y0 = (blockIdx.y * 8 + warp) * ROWS;
+    const int w = g.out_w, h = g.out_h;
+    const bool have_prev = DAMAGE && (f.prev != nullptr);
+
+    uint4 px[ROWS][QX];
+    uint32_t halo[ROWS];
+    uint32_t py[ROWS][QX];
+    uint32_t pc[RP][QX];
+    int nvq[QX];
+
+    // ---- phase 1: issue every load of this thread up front
+#pragma unroll
+    for (int q = 0; q < QX; q++) {
+        int x = bx0 + q * 128 + lane * 4;
+        int nv = w - x;
+        nvq[q] = nv >= 4 ? 4 : (nv > 0 ? 2 : 0);
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; r++) {
+        const bool rv = (y0 + r) < h;
+        const uint8_t *row = f.in + (size_t)(y0 + r) * g.in_stride;
+#pragma unroll
+        for (int q = 0; q < QX; q++) {
+            int x = bx0 + q * 128 + lane * 4;
+            px[r][q] = load_quad<HINT>(row + 4 * (size_t)x, rv ? nvq[q] : 0);
+        }
+        halo[r] = 0;
+        if (SITE == 1 && lane == 0 && bx0 > 0 && rv)
+            halo[r] = ld4<0>(row + 4 * (size_t)(bx0 - 1));
+    }
+    if (DAMAGE) {
+#pragma unroll
+        for (int r = 0; r < ROWS; r++) {
+            const bool rv = have_prev && (y0 + r) < h;
+#pragma unroll
+            for (int q = 0; q < QX; q++) {
+                int x = bx0 + q * 128 + lane * 4;
+                py[r][q] = load_word<HINT>(f.prev + (size_t)(y0 + r) * g.y_stride + x, rv ? nvq[q] : 0);
+            }
+        }
+#pragma unroll
+        for (int rp = 0; rp < RP; rp++) {
+            const int yc = (y0 >> 1) + rp;
+            const bool rv = have_prev && (y0 + 2 * rp) < h;
+#pragma unroll
+            for (int q = 0; q < QX; q++) {
+                int x = bx0 + q * 128 + lane * 4;
+                int nv = rv ? nvq[q] : 0;
+                if (FMT == 0) {
+                    pc[rp][q] = load_word<HINT>(f.prev + g.off_c0 + (size_t)yc * g.c_stride + x, nv);
+                } else {
+                    const uint8_t *pu = f.prev + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
+                    const uint8_t *pv = f.prev + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+                    uint32_t a = 0, b = 0;
+                    if (nv == 4) { a = ld2<HINT>(pu); b = ld2<HINT>(pv); }
+                    else if (nv == 2) { a = ld1(pu); b = ld1(pv); }
+                    pc[rp][q] = a | (b << 16);
+                }
+            }
+        }
+    }
+
+    // ---- phase 2: arithmetic, stores, compare
+    uint32_t diff[QX];
+#pragma unroll
+    for (int q = 0; q < QX; q++) diff[q] = 0;
+
+#pragma unroll
+    for (int rp = 0; rp < RP; rp++) {
+        uint32_t hh[2][QX][2];
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+            const int r = 2 * rp + rr;
+            const bool rv = (y0 + r) < h;
+            uint32_t uvq[QX][4];
+            uint32_t yw[QX];
+#pragma unroll
+            for (int q = 0; q < QX; q++)
+                matrix_quad(px[r][q], g, yw[q], uvq[q]);
+            uint32_t halo_uv = 0;
+            if (SITE == 1) {
+                uint32_t au = dp4a_us(halo[r], g.cu, 32768);
+                uint32_t av = dp4a_us(halo[r], g.cv, 32768);
+                halo_uv = __byte_perm(au, av, 0x7531);
+            }
+#pragma unroll
+            for (int q = 0; q < QX; q++) {
+                const int x = bx0 + q * 128 + lane * 4;
+                uint32_t left = 0;
+                if (SITE == 1) {
+                    left = __shfl_up_sync(kFull, uvq[q][3], 1);
+                    uint32_t wrap = (q > 0) ? __shfl_sync(kFull, uvq[q > 0 ? q - 1 : 0][3], 31) : halo_uv;
+                    if (lane == 0) left = wrap;
+                }
+                chroma_h<SITE>(uvq[q], left, x, w, hh[rr][q][0], hh[rr][q][1]);
+                if (rv) store_word(f.out + (size_t)(y0 + r) * g.y_stride + x, yw[q], nvq[q]);
+                if (DAMAGE) {
+                    uint32_t m = nvq[q] == 4 ? 0xffffffffu : 0x0000ffffu;
+                    diff[q] |= (yw[q] ^ py[r][q]) & m;
+                }
+            }
+        }
+        const int yc = (y0 >> 1) + rp;
+        const bool rv = (y0 + 2 * rp) < h;
+#pragma unroll
+        for (int q = 0; q < QX; q++) {
+            const int x = bx0 + q * 128 + lane * 4;
+            uint32_t cw = chroma_v<FMT>(hh[0][q][0], hh[0][q][1], hh[1][q][0], hh[1][q][1]);
+            const int nv = rv ? nvq[q] : 0;
+            if (FMT == 0) {
+                store_word(f.out + g.off_c0 + (size_t)yc * g.c_stride + x, cw, nv);
+                if (DAMAGE) diff[q] |= (cw ^ pc[rp][q]) & (nvq[q] == 4 ? 0xffffffffu : 0x0000ffffu);
+            } else {
+                uint8_t *pu = f.out + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
+                uint8_t *pv = f.out + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+                if (nv == 4) {
+                    *reinterpret_cast<unsigned short *>(pu) = (unsigned short)cw;
+                    *reinterpret_cast<unsigned short *>(pv) = (unsigned short)(cw >> 16);
+                } else if (nv == 2) {
+                    *pu = (uint8_t)cw;
+                    *pv = (uint8_t)(cw >> 16);
+                }
+                if (DAMAGE) diff[q] |= (cw ^ pc[rp][q]) & (nvq[q] == 4 ? 0xffffffffu : 0x00ff00ffu);
+            }
+        }
+    }
+
+    // ---- phase 3: per-macroblock flags
+    if (DAMAGE) {
+        __shared__ uint32_t s_mask[8][QX];
+        const bool rows_valid = y0 < h;
+#pragma unroll
+        for (int q = 0; q < QX; q++) {
+            bool d = rows_valid && nvq[q] > 0 && (diff[q] != 0 || !have_prev);
+            uint32_t m = __ballot_sync(kFull, d);
+            if (lane == 0) s_mask[warp][q] = m;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            constexpr int WPM = 8 / RP;                 // warps per macroblock row
+            bool flag = false, valid = false;
+            int bx = 0, by = 0;
+            if (lane < RP * QX * 8) {
+                const int mbrow = lane / (QX * 8);
+                const int q = (lane % (QX * 8)) / 8;
+                const int m = lane % 8;
+                uint32_t acc = 0;
+#pragma unroll
+                for (int k = 0; k < WPM; k++)
+                    acc |= s_mask[mbrow * WPM + k][q];
+                flag = ((acc >> (4 * m)) & 0xfu) != 0;
+                bx = blockIdx.x * (8 * QX) + q * 8 + m;
+                by = blockIdx.y * RP + mbrow;
+                valid = bx < g.mb_w && by < g.mb_h;
+                if (valid) f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+            }
+            uint32_t votes = __ballot_sync(kFull, valid && flag);
+            if (lane == 0) finish_count(f, votes);
+        }
+    }
+}
+
+// ---- scale kernel ---------------------------------------------------------------
+// 2-tap shrink in the RGB domain before the matrix (order as upstream's
+// chain_scale: h first when out_w*in_h <= in_w*out_h), then the same
+// matrix/chroma/damage tail.  Thread = 4 output pixels x 2 rows.
+__device__ __forceinline__ uint32_t lerp_h(uint32_t a, uint32_t b, uint32_t f)
+{
+    // per byte: (a*(256-f) + b*f) >> 8, two 16-bit lanes at a time
+    uint32_t e = ((a & 0x00ff00ffu) * (256u - f) + (b & 0x00ff00ffu) * f) >> 8;
+    uint32_t o = (((a >> 8) & 0x00ff00ffu) * (256u - f) + ((b >> 8) & 0x00ff00ffu) * f) >> 8;
+    return (e & 0x00ff00ffu) | ((o & 0x00ff00ffu) << 8);
+}
+__device__ __forceinline__ uint32_t lerp_v(uint32_t a, uint32_t b, uint32_t p)
+{
+    // per byte: a + (((b-a)*p + 32) >> 6)  ==  (a*(64-p) + b*p + 32) >> 6   (0 <= p <= 64)
+    uint32_t e = ((a & 0x00ff00ffu) * (64u - p) + (b & 0x00ff00ffu) * p + 0x00200020u) >> 6;
+    uint32_t o = (((a >> 8) & 0x00ff00ffu) * (64u - p) + ((b >> 8) & 0x00ff00ffu) * p + 0x00200020u) >> 6;
+    return (e & 0x00ff00ffu) | ((o & 0x00ff00ffu) << 8);
+}
+
+__device__ __forceinline__ uint32_t sample_px(const uint8_t *in, const SkGeom &g, int x, int o, int o2, uint32_t p)
+{
+    int x0 = x;
+    uint32_t fr = 0;
+    if (g.scale_h) {
+        int32_t acc = x * g.h_inc;
+        x0 = acc >> 16;
+        fr = (uint32_t)(acc >> 8) & 0xffu;
+    }
+    const uint8_t *r0 = in + (size_t)o * g.in_stride + 4 * (size_t)x0;
+    const uint8_t *r1 = in + (size_t)o2 * g.in_stride + 4 * (size_t)x0;
+    uint32_t a0 = ld4<0>(r0);
+    uint32_t b0 = g.scale_v ? ld4<0>(r1) : 0;
+    if (!g.scale_h)
+        return g.scale_v ? lerp_v(a0, b0, p) : a0;
+    uint32_t a1 = ld4<0>(r0 + 4);
+    uint32_t b1 = g.scale_v ? ld4<0>(r1 + 4) : 0;
+    if (!g.scale_v)
+        return lerp_h(a0, a1, fr);
+    if (g.h_first)
+        return lerp_v(lerp_h(a0, a1, fr), lerp_h(b0, b1, fr), p);
+    return lerp_h(lerp_v(a0, b0, p), lerp_v(a1, b1, p), fr);
+}
+
+template <int FMT, int SITE, bool DAMAGE>
+__global__ void __launch_bounds__(kThreads)
+sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+{
+    const SkFrame &f = batch.f[blockIdx.z];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int bx0 = blockIdx.x * 128;
+    const int y0 = (blockIdx.y * 8 + warp) * 2;
+    const int w = g.out_w, h = g.out_h;
+    const int x = bx0 + lane * 4;
+    const int nvx = (w - x) >= 4 ? 4 : ((w - x) > 0 ? 2 : 0);
+    const bool rows_valid = y0 < h;
+    const int nv = rows_valid ? nvx : 0;
+    const bool have_prev = DAMAGE && (f.prev != nullptr);
+
+    uint32_t hh[2][2];
+    uint32_t diff = 0;
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++) {
+        const int y = y0 + rr;
+        int o = y, o2 = y;
+        uint32_t p = 0;
+        if (rows_valid && g.scale_v) {
+            o = f.v_off[y];
+            p = (uint32_t)f.v_tap[y];
+            o2 = min(o + 1, g.in_h - 1);
+        }
+        uint4 q = make_uint4(0, 0, 0, 0);
+        if (nv >= 2) {
+            q.x = sample_px(f.in, g, x, o, o2, p);
+            q.y = sample_px(f.in, g, x + 1, o, o2, p);
+        }
+        if (nv == 4) {
+            q.z = sample_px(f.in, g, x + 2, o, o2, p);
+            q.w = sample_px(f.in, g, x + 3, o, o2, p);
+        }
+        uint32_t yw, uv[4];
+        matrix_quad(q, g, yw, uv);
+        uint32_t left = 0;
+        if (SITE == 1) {
+            left = __shfl_up_sync(kFull, uv[3], 1);
+            if (lane == 0) {
+                uint32_t hp = (bx0 > 0 && rows_valid) ? sample_px(f.in, g, bx0 - 1, o, o2, p) : 0;
+                uint32_t au = dp4a_us(hp, g.cu, 32768);
+                uint32_t av = dp4a_us(hp, g.cv, 32768);
+                left = __byte_perm(au, av, 0x7531);
+            }
+        }
+        chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
+        store_word(f.out + (size_t)y * g.y_stride + x, yw, nv);
+        if (DAMAGE) {
+            uint32_t pyw = load_word<0>(f.prev + (size_t)y * g.y_stride + x, have_prev ? nv : 0);
+            diff |= (yw ^ pyw) & (nvx == 4 ? 0xffffffffu : 0x0000ffffu);
+        }
+    }
+    {
+        const int yc = y0 >> 1;
+        uint32_t cw = chroma_v<FMT>(hh[0][0], hh[0][1], hh[1][0], hh[1][1]);
+        if (FMT == 0) {
+            store_word(f.out + g.off_c0 + (size_t)yc * g.c_stride + x, cw, nv);
+            if (DAMAGE) {
+                uint32_t pcw = load_word<0>(f.prev + g.off_c0 + (size_t)yc * g.c_stride + x, have_prev ? nv : 0);
+                diff |= (cw ^ pcw) & (nvx == 4 ? 0xffffffffu : 0x0000ffffu);
+            }
+        } else {
+            uint8_t *pu = f.out + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
+            uint8_t *pv = f.out + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+            if (nv == 4) {
+                *reinterpret_cast<unsigned short *>(pu) = (unsigned short)cw;
+                *reinterpret_cast<unsigned short *>(pv) = (unsigned short)(cw >> 16);
+            } else if (nv == 2) {
+                *pu = (uint8_t)cw;
+                *pv = (uint8_t)(cw >> 16);
+            }
+            if (DAMAGE) {
+                uint32_t a = 0, b = 0;
+                const uint8_t *qu = f.prev + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
+                const uint8_t *qv = f.prev + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+                if (have_prev && nv == 4) { a = ld2<0>(qu); b = ld2<0>(qv); }
+                else if (have_prev && nv == 2) { a = ld1(qu); b = ld1(qv); }
+                diff |= (cw ^ (a | (b << 16))) & (nvx == 4 ? 0xffffffffu : 0x00ff00ffu);
+            }
+        }
+    }
+    if (DAMAGE) {
+        __shared__ uint32_t s_mask[8];
+        bool d = rows_valid && nvx > 0 && (diff != 0 || !have_prev);
+        uint32_t m = __ballot_sync(kFull, d);
+        if (lane == 0) s_mask[warp] = m;
+        __syncthreads();
+        if (warp == 0) {
+            bool flag = false, valid = false;
+            if (lane < 8) {
+                uint32_t acc = 0;
+#pragma unroll
+                for (int k = 0; k < 8; k++) acc |= s_mask[k];
+                flag = ((acc >> (4 * lane)) & 0xfu) != 0;
+                int bx = blockIdx.x * 8 + lane, by = blockIdx.y;
+                valid = bx < g.mb_w && by < g.mb_h;
+                if (valid) f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+            }
+            uint32_t votes = __ballot_sync(kFull, valid && flag);
+            if (lane == 0) finish_count(f, votes);
+        }
+    }
+}
+
+template <int RP, int QX, int HINT>
+cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
+{
+    dim3 grid((g.out_w + 128 * QX - 1) / (128 * QX), (g.out_h + 16 * RP - 1) / (16 * RP), n);
+    dim3 block(kThreads);
+#define SK_CASE(FMT, SITE, DMG)                                                             \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                      \
+        sk_convert_kernel<RP, QX, FMT, SITE, DMG, HINT><<<grid, block, 0, st>>>(g, b);      \
+        return cudaGetLastError();                                                         \
+    }
+    SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
+    SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
+#undef SK_CASE
+    return cudaErrorInvalidValue;
+}
+
+}  // namespace
+
+cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant)
+{
+    switch (variant) {
+    default:
+    case 0: return launch_convert_shape<1, 1, 0>(g, b, n, st);
+    case 1: return launch_convert_shape<2, 1, 0>(g, b, n, st);
+    case 2: return launch_convert_shape<1, 2, 0>(g, b, n, st);
+    case 3: return launch_convert_shape<2, 2, 0>(g, b, n, st);
+    case 4: return launch_convert_shape<1, 1, 1>(g, b, n, st);
+    case 5: return launch_convert_shape<2, 1, 1>(g, b, n, st);
+    case 6: return launch_convert_shape<1, 2, 1>(g, b, n, st);
+    case 7: return launch_convert_shape<2, 2, 1>(g, b, n, st);
+    }
+}
+
+cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int /*variant*/)
+{
+    dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
+    dim3 block(kThreads);
+#define SK_CASE(FMT, SITE, DMG)                                                  \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {           \
+        sk_scale_kernel<FMT, SITE, DMG><<<grid, block, 0, st>>>(g, b);           \
+        return cudaGetLastError();                                              \
+    }
+    SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
+    SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
+#undef SK_CASE
+    return cudaErrorInvalidValue;
+}

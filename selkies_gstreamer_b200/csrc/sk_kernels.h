@@ -1,0 +1,45 @@
+// sk_kernels.h — internal launch interface between the session runtime and the
+// sm_100a kernels.  Not part of the C ABI.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+constexpr int SK_MAX_BATCH = 32;
+
+// Geometry + arithmetic constants shared by every frame of one launch.
+struct SkGeom {
+    int in_w, in_h;
+    int out_w, out_h;
+    int in_stride;            // bytes, multiple of 16
+    int y_stride, c_stride;   // output plane strides (GstVideoInfo default layout)
+    uint32_t off_c0, off_c1;  // byte offset of U (or UV) plane and of V plane
+    int mb_w, mb_h;
+    uint32_t cy, cu, cv;      // dp4a-packed coefficients in the input's byte order
+    int out_fmt;              // SK_OUT_*
+    int site;                 // SK_SITE_*
+    int damage;               // 0 = convert only
+    // scale path
+    int32_t h_inc;            // 16.16 edge-aligned increment
+    int h_first;              // order of the two 2-tap passes
+    int scale_h, scale_v;     // which axes actually change size
+};
+
+// Per-session pointers of one launch (all device memory).
+struct SkFrame {
+    const uint8_t *in;        // BGRx/RGBx rows, in_stride apart
+    uint8_t *out;             // packed output frame being written
+    const uint8_t *prev;      // previous packed output frame, or nullptr (all damaged)
+    uint8_t *map;             // [mb_h][mb_w]
+    uint32_t *count_out;      // damaged-block count of this frame (written by the last CTA)
+    uint32_t *scratch;        // [0] running count, [1] CTA ticket; both return to 0 at kernel end
+    const int32_t *v_off;     // scale: first source row per output row
+    const int16_t *v_tap;     // scale: second vertical tap (6-bit) per output row
+};
+
+struct SkBatch {
+    SkFrame f[SK_MAX_BATCH];
+};
+
+// variant: 0 = default. Returns the launch error (no sync).
+cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);
+cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);

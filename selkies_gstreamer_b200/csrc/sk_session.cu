@@ -1,0 +1,666 @@
+// sk_session.cu — session runtime and C ABI (include/selkies_preencode.h).
+//
+// A session is what one instance of the reference's convert stage is
+// (src/selkies/legacy/gstwebrtc_app.py:611-617 / :263-284): fixed caps, one
+// frame in → one frame out, plus the state this project adds (previous output
+// frame and damage map).  Everything a session will ever need is allocated at
+// create time; the per-frame path only enqueues copies, one kernel and events.
+//
+//   copy stream   : pinned staging slot  --cudaMemcpyAsync-->  device input slot
+//   compute stream: fused kernel (reads input slot + previous output, writes
+//                   next ring entry + damage map + count)
+//   d2h stream    : map+count (and the frame with SK_FLAG_HOST_OUTPUT) to pinned host
+#include "../../include/selkies_preencode.h"
+#include "sk_kernels.h"
+
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+namespace {
+
+constexpr int kMaxInflight = 8;
+std::atomic<uint64_t> g_launches{0};
+std::atomic<int> g_variant{0};
+thread_local std::string g_create_error;
+
+inline int ru(int v, int a) { return (v + a - 1) / a * a; }
+
+struct Slot {          // one staging slot (caller-chosen index)
+    uint8_t *h_in = nullptr;
+    uint8_t *d_in = nullptr;
+    cudaEvent_t consumed = nullptr;   // recorded after the kernel that read d_in
+    bool consumed_valid = false;
+};
+
+struct Ring {          // one output ring entry (submission order)
+    uint8_t *d_out = nullptr;
+    uint8_t *h_out = nullptr;
+    uint8_t *d_meta = nullptr;        // map bytes, then the u32 count
+    uint8_t *h_meta = nullptr;
+    cudaEvent_t h2d_start = nullptr, h2d_done = nullptr;
+    cudaEvent_t k_start = nullptr, k_done = nullptr;
+    cudaEvent_t d2h_start = nullptr, done = nullptr;
+    cudaEvent_t wait_on = nullptr;    // event sk_wait synchronises on (own `done` or a batch leader's)
+    uint64_t frame_id = 0;
+    bool valid = false;
+    bool had_h2d = false;
+    bool used = false;                // `done` has been recorded at least once
+};
+
+}  // namespace
+
+struct sk_session {
+    sk_config cfg{};
+    int dev = 0;
+    int n = 2;
+    SkGeom geom{};
+    bool scaling = false;
+    size_t in_bytes_host = 0;     // in_stride * in_h
+    int d_in_stride = 0;
+    size_t frame_bytes = 0;
+    size_t map_bytes = 0, meta_bytes = 0;
+    size_t plane_offset[3]{};
+    int plane_stride[3]{};
+    Slot slots[kMaxInflight];
+    Ring ring[kMaxInflight];
+    uint32_t *d_scratch = nullptr;
+    int32_t *d_voff = nullptr;
+    int16_t *d_vtap = nullptr;
+    cudaStream_t s_copy = nullptr, s_comp = nullptr, s_d2h = nullptr;
+    cudaEvent_t mark[2]{};
+    uint64_t seq = 0;
+    int prev_ring = -1;           // -1: no predecessor (all damaged)
+    cudaStream_t last_kernel_stream = nullptr;
+    cudaEvent_t last_kernel_event = nullptr;
+    float last_kernel_us = 0.f;
+    std::string err;
+};
+
+namespace {
+
+int fail(sk_session *s, int code, const std::string &msg)
+{
+    if (s) s->err = msg; else g_create_error = msg;
+    return code;
+}
+
+#define SK_CUDA(s, call)                                                                     \
+    do {                                                                                     \
+        cudaError_t e_ = (call);                                                             \
+        if (e_ != cudaSuccess)                                                               \
+            return fail((s), SK_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+// Integer colour matrix at 8 fractional bits: full-range RGB → limited-range
+// Y'CbCr, each entry rounded to nearest-even.
+void matrix_coeffs(int matrix, int c[3][3])
+{
+    double kr = 0.299, kb = 0.114;
+    if (matrix == SK_MATRIX_BT709) { kr = 0.2126; kb = 0.0722; }
+    else if (matrix == SK_MATRIX_BT2020) { kr = 0.2627; kb = 0.0593; }
+    const double kg = 1.0 - kr - kb;
+    const double inv255 = 1 / ((float)255);
+    const double ys = 219.0 * inv255 * 256.0, cs = 224.0 * inv255 * 256.0;
+    const double ub = 1 / (2 * (1 - kb)), vr = 1 / (2 * (1 - kr));
+    const double m[3][3] = {
+        {kr * ys, kg * ys, kb * ys},
+        {-ub * kr * cs, -ub * kg * cs, ub * (1 - kb) * cs},
+        {vr * (1 - kr) * cs, -vr * kg * cs, -vr * kb * cs}};
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+            c[i][j] = (int)std::nearbyint(m[i][j]);
+}
+
+uint32_t pack_coeffs(const int c[3], int in_fmt)
+{
+    // c = {R, G, B}; byte k of the result multiplies byte k of the pixel word.
+    uint32_t r = (uint32_t)(c[0] & 0xff), g = (uint32_t)(c[1] & 0xff), b = (uint32_t)(c[2] & 0xff);
+    if (in_fmt == SK_IN_BGRX) return b | (g << 8) | (r << 16);
+    return r | (g << 8) | (b << 16);
+}
+
+// 2-tap vertical table of the linear resampler (videoscale method=bilinear):
+// centre-aligned source position, triangle filter (stretched by out/in when
+// shrinking in the GST_LQ variant), two taps renormalised, 6-bit integer taps
+// found by a bias search so that they sum to 64.
+void vertical_taps(int in_size, int out_size, int variant, std::vector<int32_t> &off, std::vector<int16_t> &tap)
+{
+    off.resize(out_size);
+    tap.resize(out_size);
+    const double ratio = (double)in_size / out_size;
+    const double stretch = (variant == SK_SCALE_VARIANT_GST_LQ && ratio > 1.0) ? 1.0 / ratio : 1.0;
+    for (int j = 0; j < out_size; j++) {
+        double pos = (j + 0.5) / out_size * in_size - 0.5;
+        pos = std::fmin(std::fmax(pos, 0.0), (double)(in_size - 1));
+        int first = (int)std::floor(pos);
+        double w[2];
+        for (int l = 0; l < 2; l++) {
+            double a = std::fabs(pos - (first + l)) * stretch;
+            w[l] = a < 1.0 ? 1.0 - a : 0.0;
+        }
+        const double sum = w[0] + w[1];
+        w[0] /= sum;  w[1] /= sum;
+        if (first > in_size - 2) { w[1] += w[0]; w[0] = 0.0; first = in_size - 2; }
+        double lo = 0.0, hi = 1.0, bias = 0.5;
+        for (int it = 0; it < 64; it++) {
+            int s = (int)std::floor(bias + w[0] * 64.0) + (int)std::floor(bias + w[1] * 64.0);
+            if (s == 64 || lo == hi) break;
+            if (s < 64) { if (bias > lo) lo = bias; bias += (hi - lo) / 2; }
+            else        { if (bias < hi) hi = bias; bias -= (hi - lo) / 2; }
+        }
+        off[j] = first;
+        tap[j] = (int16_t)std::floor(bias + w[1] * 64.0);
+    }
+}
+
+void free_session(sk_session *s)
+{
+    if (!s) return;
+    cudaSetDevice(s->dev);
+    if (s->s_copy) cudaStreamSynchronize(s->s_copy);
+    if (s->s_comp) cudaStreamSynchronize(s->s_comp);
+    if (s->s_d2h) cudaStreamSynchronize(s->s_d2h);
+    for (int i = 0; i < kMaxInflight; i++) {
+        Slot &sl = s->slots[i];
+        if (sl.h_in) cudaFreeHost(sl.h_in);
+        if (sl.d_in) cudaFree(sl.d_in);
+        if (sl.consumed) cudaEventDestroy(sl.consumed);
+        Ring &r = s->ring[i];
+        if (r.d_out) cudaFree(r.d_out);
+        if (r.h_out) cudaFreeHost(r.h_out);
+        if (r.d_meta) cudaFree(r.d_meta);
+        if (r.h_meta) cudaFreeHost(r.h_meta);
+        cudaEvent_t evs[] = {r.h2d_start, r.h2d_done, r.k_start, r.k_done, r.d2h_start, r.done};
+        for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
+    }
+    if (s->d_scratch) cudaFree(s->d_scratch);
+    if (s->d_voff) cudaFree(s->d_voff);
+    if (s->d_vtap) cudaFree(s->d_vtap);
+    for (cudaEvent_t e : s->mark) if (e) cudaEventDestroy(e);
+    if (s->s_copy) cudaStreamDestroy(s->s_copy);
+    if (s->s_comp) cudaStreamDestroy(s->s_comp);
+    if (s->s_d2h) cudaStreamDestroy(s->s_d2h);
+    delete s;
+}
+
+int validate(const sk_config &c, std::string &why)
+{
+    auto bad_dim = [](int v) { return v < 2 || v > 8192 || (v & 1); };
+    if (bad_dim(c.in_width) || bad_dim(c.in_height)) { why = "input width/height must be even and in [2, 8192]"; return SK_ERR_ARG; }
+    if (bad_dim(c.out_width) || bad_dim(c.out_height)) { why = "output width/height must be even and in [2, 8192]"; return SK_ERR_ARG; }
+    if (c.in_stride < 4 * c.in_width) { why = "in_stride smaller than 4*in_width"; return SK_ERR_ARG; }
+    if (c.in_format != SK_IN_BGRX && c.in_format != SK_IN_RGBX) { why = "unknown in_format"; return SK_ERR_ARG; }
+    if (c.out_format != SK_OUT_NV12 && c.out_format != SK_OUT_I420) { why = "unknown out_format"; return SK_ERR_ARG; }
+    if (c.matrix < SK_MATRIX_BT601 || c.matrix > SK_MATRIX_BT2020) { why = "unknown matrix"; return SK_ERR_ARG; }
+    if (c.chroma_site != SK_SITE_NONE && c.chroma_site != SK_SITE_H_COSITED) { why = "unknown chroma_site"; return SK_ERR_ARG; }
+    if (c.n_inflight < 2 || c.n_inflight > kMaxInflight) { why = "n_inflight must be in [2, 8]"; return SK_ERR_ARG; }
+    const bool scaling = c.in_width != c.out_width || c.in_height != c.out_height;
+    if (scaling) {
+        if (c.scale_method != SK_SCALE_BILINEAR) { why = "only scale_method bilinear is supported"; return SK_ERR_UNSUPPORTED; }
+        if (c.scale_variant != SK_SCALE_VARIANT_GST_LQ && c.scale_variant != SK_SCALE_VARIANT_PLAIN_LQ) { why = "unknown scale_variant"; return SK_ERR_ARG; }
+        if ((int64_t)c.out_width * c.out_height > (int64_t)c.in_width * c.in_height) {
+            why = "enlarging (more output than input pixels) is not supported";
+            return SK_ERR_UNSUPPORTED;
+        }
+    }
+    return SK_OK;
+}
+
+int find_ring(sk_session *s, uint64_t frame_id)
+{
+    for (int i = 0; i < s->n; i++)
+        if (s->ring[i].valid && s->ring[i].frame_id == frame_id) return i;
+    return -1;
+}
+
+// Fill the launch descriptor of the next frame of `s` and advance its ring.
+// `in` is the device input pointer. Returns the ring index.
+int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
+{
+    const int ri = (int)(s->seq % (uint64_t)s->n);
+    Ring &r = s->ring[ri];
+    f.in = in;
+    f.out = r.d_out;
+    f.prev = (s->prev_ring >= 0) ? s->ring[s->prev_ring].d_out : nullptr;
+    f.map = r.d_meta;
+    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta + s->map_bytes);
+    f.scratch = s->d_scratch;
+    f.v_off = s->d_voff;
+    f.v_tap = s->d_vtap;
+    r.frame_id = frame_id;
+    r.valid = true;
+    s->prev_ring = ri;
+    s->seq++;
+    return ri;
+}
+
+cudaError_t launch(const sk_session *s, const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
+{
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (s->scaling) return sk_launch_scale(g, b, n, st, g_variant.load());
+    return sk_launch_convert(g, b, n, st, g_variant.load());
+}
+
+// Everything after the kernel for one ring entry, on the session's own d2h stream.
+int enqueue_readback(sk_session *s, int ri, cudaEvent_t kernel_done)
+{
+    Ring &r = s->ring[ri];
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    const bool damage = !(s->cfg.flags & SK_FLAG_NO_DAMAGE);
+    const bool host_out = s->cfg.flags & SK_FLAG_HOST_OUTPUT;
+    SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, kernel_done, 0));
+    if (timing) SK_CUDA(s, cudaEventRecord(r.d2h_start, s->s_d2h));
+    if (damage)
+        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, s->meta_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
+    if (host_out)
+        SK_CUDA(s, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
+    SK_CUDA(s, cudaEventRecord(r.done, s->s_d2h));
+    r.wait_on = r.done;
+    r.used = true;
+    return SK_OK;
+}
+
+int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot, uint64_t frame_id)
+{
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    const int ri_next = (int)(s->seq % (uint64_t)s->n);
+    Ring &r = s->ring[ri_next];
+    // The ring entry about to be overwritten may still be read by its D2H.
+    if (r.used) SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, r.wait_on, 0));
+    // A batch leader may have run this session's previous kernel on its stream.
+    if (s->last_kernel_stream && s->last_kernel_stream != s->s_comp)
+        SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, s->last_kernel_event, 0));
+    r.had_h2d = slot >= 0;
+    if (slot >= 0) SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, r.h2d_done, 0));
+
+    SkBatch b;
+    const int ri = stage_frame(s, d_in, frame_id, b.f[0]);
+    if (timing) SK_CUDA(s, cudaEventRecord(r.k_start, s->s_comp));
+    SK_CUDA(s, launch(s, g, b, 1, s->s_comp));
+    SK_CUDA(s, cudaEventRecord(r.k_done, s->s_comp));
+    s->last_kernel_stream = s->s_comp;
+    s->last_kernel_event = r.k_done;
+    if (slot >= 0) {
+        Slot &sl = s->slots[slot];
+        SK_CUDA(s, cudaEventRecord(sl.consumed, s->s_comp));
+        sl.consumed_valid = true;
+    }
+    return enqueue_readback(s, ri, r.k_done);
+}
+
+}  // namespace
+
+extern "C" {
+
+int sk_version(void) { return SK_ABI_VERSION; }
+
+uint64_t sk_launch_count(void) { return g_launches.load(); }
+
+int sk_set_kernel_variant(int variant)
+{
+    if (variant < 0 || variant > 15) return SK_ERR_ARG;
+    g_variant.store(variant);
+    return SK_OK;
+}
+
+int sk_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+const char *sk_last_error(sk_session *s)
+{
+    return s ? s->err.c_str() : g_create_error.c_str();
+}
+
+int sk_session_create(const sk_config *cfg_in, sk_session **out)
+{
+    if (!cfg_in || !out) return fail(nullptr, SK_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (cfg_in->struct_size != sizeof(sk_config))
+        return fail(nullptr, SK_ERR_ARG, "sk_config.struct_size does not match this library");
+    sk_config c = *cfg_in;
+    if (c.out_width == 0) c.out_width = c.in_width;
+    if (c.out_height == 0) c.out_height = c.in_height;
+    if (c.in_stride == 0) c.in_stride = 4 * c.in_width;
+    if (c.n_inflight == 0) c.n_inflight = 2;
+    if (c.scale_method == 0) c.scale_method = SK_SCALE_BILINEAR;
+    if (c.device_id < 0) c.device_id = 0;
+    std::string why;
+    int rc = validate(c, why);
+    if (rc != SK_OK) return fail(nullptr, rc, why);
+
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, SK_ERR_CUDA, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                                              " (this library has no CPU path)");
+    }
+    if (c.device_id >= ndev) return fail(nullptr, SK_ERR_ARG, "cuda-device-id out of range");
+
+    sk_session *s = new (std::nothrow) sk_session();
+    if (!s) return fail(nullptr, SK_ERR_NOMEM, "out of host memory");
+    s->cfg = c;
+    s->dev = c.device_id;
+    s->n = c.n_inflight;
+    s->scaling = c.in_width != c.out_width || c.in_height != c.out_height;
+
+#define SK_TRY(call)                                                                           \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess) {                                                               \
+            g_create_error = std::string(#call) + ": " + cudaGetErrorString(e_);               \
+            free_session(s);                                                                   \
+            return SK_ERR_CUDA;                                                                \
+        }                                                                                      \
+    } while (0)
+
+    SK_TRY(cudaSetDevice(s->dev));
+    // geometry (GstVideoInfo default layout)
+    SkGeom &g = s->geom;
+    g.in_w = c.in_width;  g.in_h = c.in_height;
+    g.out_w = c.out_width;  g.out_h = c.out_height;
+    const int h2 = ru(g.out_h, 2);
+    g.y_stride = ru(g.out_w, 4);
+    if (c.out_format == SK_OUT_I420) {
+        g.c_stride = ru(ru(g.out_w, 2) / 2, 4);
+        g.off_c0 = (uint32_t)g.y_stride * h2;
+        g.off_c1 = g.off_c0 + (uint32_t)g.c_stride * (h2 / 2);
+        s->frame_bytes = (size_t)g.off_c1 + (size_t)g.c_stride * (h2 / 2);
+        s->plane_offset[0] = 0; s->plane_offset[1] = g.off_c0; s->plane_offset[2] = g.off_c1;
+        s->plane_stride[0] = g.y_stride; s->plane_stride[1] = g.c_stride; s->plane_stride[2] = g.c_stride;
+    } else {
+        g.c_stride = g.y_stride;
+        g.off_c0 = (uint32_t)g.y_stride * h2;
+        g.off_c1 = 0;
+        s->frame_bytes = (size_t)g.off_c0 + (size_t)g.c_stride * (h2 / 2);
+        s->plane_offset[0] = 0; s->plane_offset[1] = g.off_c0; s->plane_offset[2] = 0;
+        s->plane_stride[0] = g.y_stride; s->plane_stride[1] = g.c_stride; s->plane_stride[2] = 0;
+    }
+    g.mb_w = (g.out_w + 15) / 16;
+    g.mb_h = (g.out_h + 15) / 16;
+    int m[3][3];
+    matrix_coeffs(c.matrix, m);
+    g.cy = pack_coeffs(m[0], c.in_format);
+    g.cu = pack_coeffs(m[1], c.in_format);
+    g.cv = pack_coeffs(m[2], c.in_format);
+    g.out_fmt = c.out_format;
+    g.site = c.chroma_site;
+    g.damage = (c.flags & SK_FLAG_NO_DAMAGE) ? 0 : 1;
+    g.scale_h = g.in_w != g.out_w;
+    g.scale_v = g.in_h != g.out_h;
+    g.h_inc = g.out_w > 1 ? (int32_t)((((int64_t)g.in_w - 1) << 16) / (g.out_w - 1) - 1) : 0;
+    g.h_first = ((int64_t)g.out_w * g.in_h <= (int64_t)g.in_w * g.out_h) ? 1 : 0;
+    s->d_in_stride = ru(c.in_stride, 16);
+    g.in_stride = s->d_in_stride;
+    s->in_bytes_host = (size_t)c.in_stride * c.in_height;
+    s->map_bytes = (size_t)ru(g.mb_w * g.mb_h, 4);
+    s->meta_bytes = s->map_bytes + 4;
+
+    SK_TRY(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
+    SK_TRY(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
+    SK_TRY(cudaStreamCreateWithFlags(&s->s_d2h, cudaStreamNonBlocking));
+    const unsigned evflags = (c.flags & SK_FLAG_TIMING) ? cudaEventDefault : cudaEventDisableTiming;
+    for (int i = 0; i < s->n; i++) {
+        Slot &sl = s->slots[i];
+        SK_TRY(cudaHostAlloc((void **)&sl.h_in, s->in_bytes_host, cudaHostAllocDefault));
+        SK_TRY(cudaMalloc((void **)&sl.d_in, (size_t)s->d_in_stride * c.in_height + 16));
+        SK_TRY(cudaEventCreateWithFlags(&sl.consumed, cudaEventDisableTiming));
+        Ring &r = s->ring[i];
+        SK_TRY(cudaMalloc((void **)&r.d_out, s->frame_bytes));
+        SK_TRY(cudaMemset(r.d_out, 0, s->frame_bytes));
+        SK_TRY(cudaMalloc((void **)&r.d_meta, s->meta_bytes));
+        SK_TRY(cudaMemset(r.d_meta, 0, s->meta_bytes));
+        SK_TRY(cudaHostAlloc((void **)&r.h_meta, s->meta_bytes, cudaHostAllocDefault));
+        std::memset(r.h_meta, 0, s->meta_bytes);
+        if (c.flags & SK_FLAG_HOST_OUTPUT)
+            SK_TRY(cudaHostAlloc((void **)&r.h_out, s->frame_bytes, cudaHostAllocDefault));
+        cudaEvent_t *evs[] = {&r.h2d_start, &r.h2d_done, &r.k_start, &r.k_done, &r.d2h_start, &r.done};
+        for (cudaEvent_t *ev : evs) SK_TRY(cudaEventCreateWithFlags(ev, evflags));
+    }
+    SK_TRY(cudaMalloc((void **)&s->d_scratch, 256));
+    SK_TRY(cudaMemset(s->d_scratch, 0, 256));
+    for (cudaEvent_t &ev : s->mark) SK_TRY(cudaEventCreate(&ev));
+    if (s->scaling) {
+        std::vector<int32_t> off;
+        std::vector<int16_t> tap;
+        vertical_taps(g.in_h, g.out_h, c.scale_variant, off, tap);
+        SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
+        SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
+        SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        SK_TRY(cudaMemcpy(s->d_vtap, tap.data(), tap.size() * sizeof(int16_t), cudaMemcpyHostToDevice));
+    }
+    SK_TRY(cudaDeviceSynchronize());
+#undef SK_TRY
+    *out = s;
+    return SK_OK;
+}
+
+int sk_session_destroy(sk_session *s)
+{
+    if (!s) return SK_ERR_ARG;
+    free_session(s);
+    return SK_OK;
+}
+
+int sk_get_input_staging(sk_session *s, int slot, void **host_ptr, size_t *bytes)
+{
+    if (!s || !host_ptr) return SK_ERR_ARG;
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    *host_ptr = s->slots[slot].h_in;
+    if (bytes) *bytes = s->in_bytes_host;
+    return SK_OK;
+}
+
+int sk_get_device_input(sk_session *s, int slot, void **dptr, size_t *stride)
+{
+    if (!s || !dptr) return SK_ERR_ARG;
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    *dptr = s->slots[slot].d_in;
+    if (stride) *stride = (size_t)s->d_in_stride;
+    return SK_OK;
+}
+
+int sk_upload(sk_session *s, int slot, const void *src, size_t src_stride)
+{
+    if (!s || !src) return SK_ERR_ARG;
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    const size_t row = (size_t)4 * s->cfg.in_width;
+    if (src_stride == 0) src_stride = row;
+    if (src_stride < row) return fail(s, SK_ERR_ARG, "src_stride smaller than a row");
+    uint8_t *dst = s->slots[slot].h_in;
+    if (src_stride == (size_t)s->cfg.in_stride) {
+        std::memcpy(dst, src, s->in_bytes_host - (src_stride - row));
+    } else {
+        for (int y = 0; y < s->cfg.in_height; y++)
+            std::memcpy(dst + (size_t)y * s->cfg.in_stride, (const uint8_t *)src + (size_t)y * src_stride, row);
+    }
+    return SK_OK;
+}
+
+int sk_submit(sk_session *s, int slot, uint64_t frame_id)
+{
+    if (!s) return SK_ERR_ARG;
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    Slot &sl = s->slots[slot];
+    Ring &r = s->ring[s->seq % (uint64_t)s->n];
+    // The device copy of this slot may still be read by an earlier kernel.
+    if (sl.consumed_valid) SK_CUDA(s, cudaStreamWaitEvent(s->s_copy, sl.consumed, 0));
+    if (timing) SK_CUDA(s, cudaEventRecord(r.h2d_start, s->s_copy));
+    if (s->d_in_stride == s->cfg.in_stride) {
+        SK_CUDA(s, cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes_host, cudaMemcpyHostToDevice, s->s_copy));
+    } else {
+        SK_CUDA(s, cudaMemcpy2DAsync(sl.d_in, s->d_in_stride, sl.h_in, s->cfg.in_stride,
+                                     (size_t)4 * s->cfg.in_width, s->cfg.in_height,
+                                     cudaMemcpyHostToDevice, s->s_copy));
+    }
+    SK_CUDA(s, cudaEventRecord(r.h2d_done, s->s_copy));
+    return submit_common(s, s->geom, sl.d_in, slot, frame_id);
+}
+
+int sk_submit_device(sk_session *s, const void *dptr, size_t stride, uint64_t frame_id)
+{
+    if (!s || !dptr) return SK_ERR_ARG;
+    if (stride == 0) stride = (size_t)s->d_in_stride;
+    if (((uintptr_t)dptr & 15) || (stride & 15)) return fail(s, SK_ERR_ALIGN, "device frame pointer and stride must be 16-byte aligned");
+    if (stride < (size_t)4 * s->cfg.in_width) return fail(s, SK_ERR_ARG, "stride smaller than a row");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SkGeom g = s->geom;
+    g.in_stride = (int)stride;
+    return submit_common(s, g, (const uint8_t *)dptr, -1, frame_id);
+}
+
+int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t stride, uint64_t frame_id)
+{
+    if (!ss || !dptrs || n < 1) return SK_ERR_ARG;
+    sk_session *L = ss[0];
+    if (!L) return SK_ERR_ARG;
+    if (n > SK_MAX_BATCH) return fail(L, SK_ERR_ARG, "batch larger than SK_MAX_BATCH (32)");
+    if (stride == 0) stride = (size_t)L->d_in_stride;
+    if (stride & 15) return fail(L, SK_ERR_ALIGN, "stride must be 16-byte aligned");
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        if (!s || !dptrs[i]) return fail(L, SK_ERR_ARG, "null session or frame in batch");
+        if ((uintptr_t)dptrs[i] & 15) return fail(L, SK_ERR_ALIGN, "device frame pointers must be 16-byte aligned");
+        const sk_config &a = L->cfg, &b = s->cfg;
+        if (s->dev != L->dev || a.in_width != b.in_width || a.in_height != b.in_height ||
+            a.out_width != b.out_width || a.out_height != b.out_height || a.in_format != b.in_format ||
+            a.out_format != b.out_format || a.matrix != b.matrix || a.chroma_site != b.chroma_site ||
+            a.scale_variant != b.scale_variant || ((a.flags ^ b.flags) & SK_FLAG_NO_DAMAGE))
+            return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
+        for (int j = 0; j < i; j++)
+            if (ss[j] == s) return fail(L, SK_ERR_STATE, "a session appears twice in one batch");
+    }
+    SK_CUDA(L, cudaSetDevice(L->dev));
+    const bool timing = L->cfg.flags & SK_FLAG_TIMING;
+    SkGeom g = L->geom;
+    g.in_stride = (int)stride;
+    SkBatch b;
+    int ris[SK_MAX_BATCH];
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        Ring &r = s->ring[s->seq % (uint64_t)s->n];
+        if (r.used) SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, r.wait_on, 0));
+        if (s->last_kernel_stream && s->last_kernel_stream != L->s_comp)
+            SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, s->last_kernel_event, 0));
+        r.had_h2d = false;
+        ris[i] = stage_frame(s, (const uint8_t *)dptrs[i], frame_id, b.f[i]);
+    }
+    Ring &lr = L->ring[ris[0]];
+    if (timing) SK_CUDA(L, cudaEventRecord(lr.k_start, L->s_comp));
+    SK_CUDA(L, launch(L, g, b, n, L->s_comp));
+    SK_CUDA(L, cudaEventRecord(lr.k_done, L->s_comp));
+    // Read-back of every member rides on the leader's d2h stream; one event closes the batch.
+    SK_CUDA(L, cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
+    if (timing) SK_CUDA(L, cudaEventRecord(lr.d2h_start, L->s_d2h));
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        Ring &r = s->ring[ris[i]];
+        if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE))
+            SK_CUDA(L, cudaMemcpyAsync(r.h_meta, r.d_meta, s->meta_bytes, cudaMemcpyDeviceToHost, L->s_d2h));
+        if (s->cfg.flags & SK_FLAG_HOST_OUTPUT)
+            SK_CUDA(L, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, L->s_d2h));
+    }
+    SK_CUDA(L, cudaEventRecord(lr.done, L->s_d2h));
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        Ring &r = s->ring[ris[i]];
+        r.wait_on = lr.done;
+        r.used = true;
+        s->last_kernel_stream = L->s_comp;
+        s->last_kernel_event = lr.k_done;
+    }
+    return SK_OK;
+}
+
+int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
+{
+    if (!s) return SK_ERR_ARG;
+    const int ri = find_ring(s, frame_id);
+    if (ri < 0) return fail(s, SK_ERR_STATE, "unknown frame id (never submitted, or its ring entry was reused)");
+    Ring &r = s->ring[ri];
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaEventSynchronize(r.wait_on));
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    const bool own_events = r.wait_on == r.done;
+    if (timing && own_events) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r.k_start, r.k_done) == cudaSuccess) s->last_kernel_us = ms * 1e3f;
+        else cudaGetLastError();
+    }
+    if (out) {
+        std::memset(out, 0, sizeof(*out));
+        out->frame_id = frame_id;
+        out->dev_frame = r.d_out;
+        out->host_frame = (s->cfg.flags & SK_FLAG_HOST_OUTPUT) ? r.h_out : nullptr;
+        out->frame_bytes = s->frame_bytes;
+        for (int i = 0; i < 3; i++) {
+            out->plane_offset[i] = s->plane_offset[i];
+            out->plane_stride[i] = s->plane_stride[i];
+        }
+        out->mb_w = s->geom.mb_w;
+        out->mb_h = s->geom.mb_h;
+        if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) {
+            out->host_damage_map = r.h_meta;
+            out->dev_damage_map = r.d_meta;
+            uint32_t cnt;
+            std::memcpy(&cnt, r.h_meta + s->map_bytes, 4);
+            out->damaged_count = cnt;
+        }
+        if (timing && own_events) {
+            float ms = 0.f;
+            out->kernel_us = s->last_kernel_us;
+            if (r.had_h2d && cudaEventElapsedTime(&ms, r.h2d_start, r.h2d_done) == cudaSuccess) out->h2d_us = ms * 1e3f;
+            if (cudaEventElapsedTime(&ms, r.d2h_start, r.done) == cudaSuccess) out->d2h_us = ms * 1e3f;
+            cudaGetLastError();
+        }
+    }
+    return SK_OK;
+}
+
+int sk_last_kernel_us(sk_session *s, float *us)
+{
+    if (!s || !us) return SK_ERR_ARG;
+    if (!(s->cfg.flags & SK_FLAG_TIMING)) return fail(s, SK_ERR_STATE, "session was created without SK_FLAG_TIMING");
+    *us = s->last_kernel_us;
+    return SK_OK;
+}
+
+int sk_marker_record(sk_session *s, int which)
+{
+    if (!s || which < 0 || which > 1) return SK_ERR_ARG;
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaEventRecord(s->mark[which], s->s_comp));
+    return SK_OK;
+}
+
+int sk_marker_elapsed_us(sk_session *s, float *us)
+{
+    if (!s || !us) return SK_ERR_ARG;
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaEventSynchronize(s->mark[1]));
+    float ms = 0.f;
+    SK_CUDA(s, cudaEventElapsedTime(&ms, s->mark[0], s->mark[1]));
+    *us = ms * 1e3f;
+    return SK_OK;
+}
+
+int sk_reset_history(sk_session *s)
+{
+    if (!s) return SK_ERR_ARG;
+    s->prev_ring = -1;
+    return SK_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,223 @@
+"""Per-desktop session: the Python face of one sk_session.
+
+One session is what one instance of the reference's convert stage is
+(src/selkies/legacy/gstwebrtc_app.py:611-617 videoconvert / :263-284
+cudaupload+cudaconvert): fixed caps, frames in, NV12/I420 frames out — plus the
+per-16x16 damage map.  All pixel work happens in libselkies_preencode.so on the
+GPU; this file only moves pointers.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _abi, colorimetry as _col
+
+IN_FORMATS = {"BGRX": _abi.SK_IN_BGRX, "BGRA": _abi.SK_IN_BGRX, "RGBX": _abi.SK_IN_RGBX, "RGBA": _abi.SK_IN_RGBX}
+OUT_FORMATS = {"NV12": _abi.SK_OUT_NV12, "I420": _abi.SK_OUT_I420}
+_ERR_NAMES = {-1: "SK_ERR_ARG", -2: "SK_ERR_CUDA", -3: "SK_ERR_ALIGN", -4: "SK_ERR_STATE",
+              -5: "SK_ERR_UNSUPPORTED", -6: "SK_ERR_NOMEM"}
+
+
+class PreencodeError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"{_ERR_NAMES.get(code, code)}: {message}")
+        self.code = code
+
+
+def frame_layout(width: int, height: int, out_format: str):
+    """GstVideoInfo default layout: (size, offsets[3], strides[3])."""
+    ru = lambda v, a: (v + a - 1) // a * a
+    h2 = ru(height, 2)
+    ys = ru(width, 4)
+    if out_format.upper() == "I420":
+        cs = ru(ru(width, 2) // 2, 4)
+        off = [0, ys * h2, ys * h2 + cs * (h2 // 2)]
+        return off[2] + cs * (h2 // 2), off, [ys, cs, cs]
+    off = [0, ys * h2, 0]
+    return off[1] + ys * (h2 // 2), off, [ys, ys, 0]
+
+
+@dataclass
+class FrameResult:
+    frame_id: int
+    frame: np.ndarray | None        # packed output frame (pinned host view) or None
+    damage_map: np.ndarray | None   # uint8 [mb_h, mb_w]
+    damaged_count: int
+    dev_frame: int                  # device address of the packed frame
+    dev_damage_map: int
+    plane_offset: tuple
+    plane_stride: tuple
+    h2d_us: float
+    kernel_us: float
+    d2h_us: float
+
+
+class PreencodeSession:
+    def __init__(self, width: int, height: int, *, in_format: str = "BGRx", out_format: str = "NV12",
+                 out_width: int | None = None, out_height: int | None = None,
+                 colorimetry=None, chroma_site=None, device_id: int = -1, n_inflight: int = 2,
+                 in_stride: int = 0, damage: bool = True, host_output: bool = True, timing: bool = False,
+                 scale_variant: int = _abi.SK_SCALE_VARIANT_GST_LQ):
+        self._lib = _abi.load()
+        self._h = ctypes.c_void_p()
+        if in_format.upper() not in IN_FORMATS:
+            raise ValueError(f"unsupported input format {in_format!r}")
+        if out_format.upper() not in OUT_FORMATS:
+            raise ValueError(f"unsupported output format {out_format!r}")
+        self.width, self.height = int(width), int(height)
+        self.out_width = int(out_width or width)
+        self.out_height = int(out_height or height)
+        self.in_format, self.out_format = in_format, out_format.upper()
+        self.matrix, self.site = _col.resolve(self.out_height, colorimetry, chroma_site)
+        self.in_stride = int(in_stride) or 4 * self.width
+        self.n_inflight = n_inflight
+        flags = (0 if damage else _abi.SK_FLAG_NO_DAMAGE) | (_abi.SK_FLAG_HOST_OUTPUT if host_output else 0) \
+            | (_abi.SK_FLAG_TIMING if timing else 0)
+        self.flags = flags
+        cfg = _abi.SkConfig(ctypes.sizeof(_abi.SkConfig), device_id, self.width, self.height, self.in_stride,
+                            IN_FORMATS[in_format.upper()], self.out_width, self.out_height,
+                            OUT_FORMATS[self.out_format], self.matrix, self.site, _abi.SK_SCALE_BILINEAR,
+                            scale_variant, n_inflight, flags)
+        rc = self._lib.sk_session_create(ctypes.byref(cfg), ctypes.byref(self._h))
+        if rc != _abi.SK_OK:
+            self._h = ctypes.c_void_p()
+            raise PreencodeError(rc, (self._lib.sk_last_error(None) or b"").decode())
+        self.frame_bytes, self.plane_offset, self.plane_stride = frame_layout(self.out_width, self.out_height, self.out_format)
+        self._next_id = 0
+
+    # -- plumbing ---------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != _abi.SK_OK:
+            raise PreencodeError(rc, (self._lib.sk_last_error(self._h) or b"").decode())
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.sk_session_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    # -- frame path -------------------------------------------------------
+    def staging(self, slot: int) -> np.ndarray:
+        """Pinned staging of `slot` as uint8 [H, in_stride] — capture straight into it."""
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        self._check(self._lib.sk_get_input_staging(self._h, slot, ctypes.byref(p), ctypes.byref(n)))
+        buf = (ctypes.c_uint8 * n.value).from_address(p.value)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(self.height, self.in_stride)
+
+    def device_input(self, slot: int) -> tuple[int, int]:
+        p, st = ctypes.c_void_p(), ctypes.c_size_t()
+        self._check(self._lib.sk_get_device_input(self._h, slot, ctypes.byref(p), ctypes.byref(st)))
+        return p.value, st.value
+
+    def upload(self, slot: int, frame: np.ndarray):
+        """Copy a [H, W, 4] uint8 frame (row-strided views allowed) into staging."""
+        if frame.dtype != np.uint8 or frame.ndim != 3 or frame.shape != (self.height, self.width, 4):
+            raise ValueError(f"expected uint8 [{self.height}, {self.width}, 4], got {frame.dtype} {frame.shape}")
+        if frame.strides[2] != 1 or frame.strides[1] != 4:
+            frame = np.ascontiguousarray(frame)
+        self._check(self._lib.sk_upload(self._h, slot, frame.ctypes.data, frame.strides[0]))
+
+    def submit(self, slot: int, frame_id: int | None = None) -> int:
+        fid = self._take_id(frame_id)
+        self._check(self._lib.sk_submit(self._h, slot, fid))
+        return fid
+
+    def submit_device(self, dptr: int, stride: int = 0, frame_id: int | None = None) -> int:
+        fid = self._take_id(frame_id)
+        self._check(self._lib.sk_submit_device(self._h, ctypes.c_void_p(dptr), stride, fid))
+        return fid
+
+    def _take_id(self, frame_id):
+        if frame_id is None:
+            frame_id = self._next_id
+        self._next_id = int(frame_id) + 1
+        return int(frame_id)
+
+    def wait(self, frame_id: int) -> FrameResult:
+        r = _abi.SkResult()
+        self._check(self._lib.sk_wait(self._h, frame_id, ctypes.byref(r)))
+        frame = dmap = None
+        if r.host_frame:
+            buf = (ctypes.c_uint8 * r.frame_bytes).from_address(r.host_frame)
+            frame = np.frombuffer(buf, dtype=np.uint8)
+        if r.host_damage_map:
+            buf = (ctypes.c_uint8 * (r.mb_w * r.mb_h)).from_address(r.host_damage_map)
+            dmap = np.frombuffer(buf, dtype=np.uint8).reshape(r.mb_h, r.mb_w)
+        return FrameResult(r.frame_id, frame, dmap, r.damaged_count, r.dev_frame or 0, r.dev_damage_map or 0,
+                           tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us)
+
+    def convert(self, frame: np.ndarray, slot: int = 0) -> FrameResult:
+        """Synchronous convenience: upload → submit → wait."""
+        self.upload(slot, frame)
+        return self.wait(self.submit(slot))
+
+    def reset_history(self):
+        self._check(self._lib.sk_reset_history(self._h))
+
+    def marker(self, which: int):
+        self._check(self._lib.sk_marker_record(self._h, which))
+
+    def marker_elapsed_us(self) -> float:
+        us = ctypes.c_float()
+        self._check(self._lib.sk_marker_elapsed_us(self._h, ctypes.byref(us)))
+        return us.value
+
+    def last_kernel_us(self) -> float:
+        us = ctypes.c_float()
+        self._check(self._lib.sk_last_kernel_us(self._h, ctypes.byref(us)))
+        return us.value
+
+    def planes(self, packed: np.ndarray):
+        """Views (Y, U, V) of a packed output frame; for NV12 U and V are strided views of UV."""
+        w, h = self.out_width, self.out_height
+        h2, w2 = (h + 1) & ~1, (w + 1) // 2
+        off, st = self.plane_offset, self.plane_stride
+        y = packed[off[0]:off[0] + st[0] * h2].reshape(h2, st[0])[:h, :w]
+        if self.out_format == "I420":
+            u = packed[off[1]:off[1] + st[1] * (h2 // 2)].reshape(h2 // 2, st[1])[:, :w2]
+            v = packed[off[2]:off[2] + st[2] * (h2 // 2)].reshape(h2 // 2, st[2])[:, :w2]
+            return y, u, v
+        uv = packed[off[1]:off[1] + st[1] * (h2 // 2)].reshape(h2 // 2, st[1])[:, :2 * w2]
+        return y, uv[:, 0::2], uv[:, 1::2]
+
+
+def batch_submit(sessions: list[PreencodeSession], dptrs: list[int], stride: int = 0, frame_id: int = 0):
+    """One kernel launch over several sessions of identical configuration (same GPU)."""
+    n = len(sessions)
+    if n == 0 or n != len(dptrs):
+        raise ValueError("sessions and dptrs must be non-empty and of equal length")
+    lib = sessions[0]._lib
+    hs = (ctypes.c_void_p * n)(*[s._h.value for s in sessions])
+    ps = (ctypes.c_void_p * n)(*dptrs)
+    rc = lib.sk_batch_submit(hs, n, ps, stride, frame_id)
+    if rc != _abi.SK_OK:
+        raise PreencodeError(rc, (lib.sk_last_error(sessions[0]._h) or b"").decode())
+    for s in sessions:
+        s._next_id = frame_id + 1
+    return frame_id
+
+
+def launch_count() -> int:
+    return int(_abi.load().sk_launch_count())
+
+
+def device_count() -> int:
+    return int(_abi.load().sk_device_count())

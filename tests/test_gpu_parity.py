@@ -1,0 +1,332 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes →
+libselkies_preencode.so), must be bit-exact with the CPU oracle on the same
+inputs, and exactly equal on the damage map.  Run on the B200 box:
+    python -m pytest tests -m gpu -x -q
+"""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+
+from oracle import cpu_oracle as o
+from selkies_gstreamer_b200 import PreencodeError, PreencodeSession, _abi, batch_submit, launch_count, synth
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+IN_NAMES = {0: "BGRx", 1: "RGBx"}
+OUT_NAMES = {0: "NV12", 1: "I420"}
+
+
+def oracle_frame(frame, sess_kw, out_w=None, out_h=None, variant=0):
+    return o.convert(frame, out_w, out_h,
+                     in_fmt={"BGRx": 0, "RGBx": 1, "BGRA": 0, "RGBA": 1}[sess_kw.get("in_format", "BGRx")],
+                     out_fmt={"NV12": 0, "I420": 1}[sess_kw.get("out_format", "NV12")],
+                     matrix=sess_kw["colorimetry"], chroma_site=sess_kw["chroma_site"],
+                     scale_variant=variant, n_threads=8)
+
+
+def check_sequence(frames, w, h, *, out_w=None, out_h=None, variant=0, n_inflight=2, **kw):
+    """Run frames through one session; compare every output and map with the oracle."""
+    kw.setdefault("colorimetry", 1)
+    kw.setdefault("chroma_site", 1)
+    ow, oh = out_w or w, out_h or h
+    fmt = {"NV12": 0, "I420": 1}[kw.get("out_format", "NV12")]
+    with PreencodeSession(w, h, out_width=out_w, out_height=out_h, n_inflight=n_inflight,
+                          scale_variant=variant, **kw) as s:
+        prev = None
+        for i, f in enumerate(frames):
+            r = s.convert(f, slot=i % n_inflight)
+            exp = oracle_frame(f, kw, out_w, out_h, variant)
+            assert r.frame.shape == exp.shape
+            if not (r.frame == exp).all():
+                bad = np.flatnonzero(r.frame != exp)
+                raise AssertionError(f"frame {i}: {bad.size} bytes differ, first at {bad[:8]} "
+                                     f"got {r.frame[bad[:8]]} want {exp[bad[:8]]}")
+            em, en = o.damage(ow, oh, fmt, exp, prev)
+            assert (r.damage_map == em).all(), f"frame {i}: damage map differs"
+            assert r.damaged_count == en
+            prev = exp
+
+
+def rand_frame(w, h, seed):
+    return np.random.default_rng(seed).integers(0, 256, (h, w, 4), dtype=np.uint8)
+
+
+# --------------------------------------------------------------------------
+def test_known_answer_colours_on_gpu():
+    kat = json.load(open(os.path.join(GOLDEN, "kat_colours.json")))
+    for m in range(3):
+        for site in (0, 1):
+            with PreencodeSession(16, 4, colorimetry=m, chroma_site=site, out_format="I420") as s:
+                for vec in kat["vectors"]:
+                    f = np.empty((4, 16, 4), np.uint8)
+                    r, g, b = vec["rgb"]
+                    f[..., 0], f[..., 1], f[..., 2], f[..., 3] = b, g, r, 0x5A
+                    res = s.convert(f)
+                    y, u, v = s.planes(res.frame)
+                    ey, eu, ev = vec["yuv"][m]
+                    assert (y == ey).all() and (u == eu).all() and (v == ev).all(), (vec, m, site)
+
+
+def test_frozen_fixtures_on_gpu():
+    z = np.load(os.path.join(GOLDEN, "frozen_small.npz"))
+    for i, (w, h, ow, oh, inf, outf, m, site, var, _seed) in enumerate(z["cases"].tolist()):
+        with PreencodeSession(w, h, out_width=ow, out_height=oh, in_format=IN_NAMES[inf], out_format=OUT_NAMES[outf],
+                              colorimetry=m, chroma_site=site, scale_variant=var) as s:
+            a = s.convert(z[f"in0_{i}"], 0)
+            assert (a.frame == z[f"out0_{i}"]).all(), f"case {i} frame 0"
+            assert a.damage_map.all()
+            b = s.convert(z[f"in1_{i}"], 1)
+            assert (b.frame == z[f"out1_{i}"]).all(), f"case {i} frame 1"
+            assert (b.damage_map == z[f"map1_{i}"]).all(), f"case {i} map"
+            assert b.damaged_count == int(z[f"map1_{i}"].sum())
+
+
+@pytest.mark.parametrize("w,h", [(2, 2), (4, 2), (6, 4), (8, 16), (34, 18), (126, 30), (128, 16), (130, 34),
+                                 (254, 24), (258, 50), (640, 360), (1366, 768)])
+def test_small_and_ragged_sizes_all_modes(w, h):
+    f0 = rand_frame(w, h, w * 7 + h)
+    f1 = f0.copy()
+    f1[h // 2, w // 2, :3] ^= 0x3C
+    for m in range(3):
+        for site in (0, 1):
+            for out_format in ("NV12", "I420"):
+                in_format = "RGBx" if (m + site) % 2 else "BGRx"
+                check_sequence([f0, f1, f1], w, h, colorimetry=m, chroma_site=site, out_format=out_format,
+                               in_format=in_format)
+
+
+@pytest.mark.parametrize("variant", range(8))
+def test_every_kernel_variant_is_bit_exact(variant):
+    lib = _abi.load()
+    try:
+        assert lib.sk_set_kernel_variant(variant) == 0
+        for (w, h) in [(258, 50), (1920, 1080), (1366, 768)]:
+            f0 = rand_frame(w, h, 100 + variant)
+            f1 = synth.mutate(f0, 0.05, seed=variant, aligned=False)
+            for out_format in ("NV12", "I420"):
+                for site in (0, 1):
+                    check_sequence([f0, f1], w, h, out_format=out_format, chroma_site=site)
+    finally:
+        lib.sk_set_kernel_variant(0)
+
+
+@pytest.mark.parametrize("name,w,h,fmt", [("1080p-I420", 1920, 1080, "I420"), ("4K-NV12", 3840, 2160, "NV12"),
+                                          ("8K-I420", 7680, 4320, "I420")])
+def test_baseline_configs_full_size(name, w, h, fmt):
+    f0 = synth.desktop(w, h)
+    f1 = synth.mutate(f0, 0.005, seed=3, aligned=False)     # sparse damage (config 5)
+    f2 = synth.noise(w, h)
+    check_sequence([f0, f1, f1, f2], w, h, out_format=fmt)
+
+
+def test_default_colorimetry_by_height():
+    # upstream set_default_colorimetry: <=576 bt601/none, <2160 bt709/h-cosited, >=2160 bt2020/h-cosited
+    for (w, h, m, site) in [(720, 576, 0, 0), (1280, 720, 1, 1), (3840, 2160, 2, 1)]:
+        f = rand_frame(w, h, h)
+        with PreencodeSession(w, h) as s:
+            assert (s.matrix, s.site) == (m, site)
+            r = s.convert(f)
+        assert (r.frame == o.convert(f, matrix=m, chroma_site=site, n_threads=8)).all()
+
+
+def test_bars_and_checkerboard_exercise_chroma_filters():
+    f = synth.bars(1920, 1080)
+    for site in (0, 1):
+        check_sequence([f], 1920, 1080, chroma_site=site, out_format="I420")
+
+
+def test_padding_byte_does_not_matter():
+    f = rand_frame(256, 64, 1)
+    g = f.copy()
+    g[..., 3] = 0
+    with PreencodeSession(256, 64) as s:
+        a = s.convert(f, 0)
+        fa = a.frame.copy()
+        b = s.convert(g, 1)
+        assert (fa == b.frame).all()
+        assert b.damaged_count == 0 and not b.damage_map.any()
+
+
+def test_strided_capture_rows():
+    big = rand_frame(300, 80, 2)
+    view = big[5:69, 10:266]                  # 256x64 region of a larger framebuffer
+    with PreencodeSession(256, 64, in_stride=4 * 256 + 40) as s:     # staging stride not a multiple of 16
+        st = s.staging(0)
+        assert st.shape == (64, 4 * 256 + 40)
+        s.upload(0, view)
+        r = s.wait(s.submit(0))
+    assert (r.frame == o.convert(np.ascontiguousarray(view), n_threads=2)).all()
+
+
+def test_idempotence_and_reset_history():
+    f = synth.desktop(1920, 1080)
+    with PreencodeSession(1920, 1080, n_inflight=3) as s:
+        r0 = s.convert(f, 0)
+        assert r0.damage_map.all() and r0.damaged_count == 120 * 68
+        r1 = s.convert(f, 1)
+        assert r1.damaged_count == 0 and not r1.damage_map.any()
+        s.reset_history()
+        r2 = s.convert(f, 2)
+        assert r2.damage_map.all() and r2.damaged_count == 120 * 68
+        r3 = s.convert(f, 0)
+        assert r3.damaged_count == 0
+
+
+def test_frames_in_flight_ring():
+    w, h, n = 640, 360, 4
+    frames = [rand_frame(w, h, 50)]
+    for i in range(7):
+        frames.append(synth.mutate(frames[-1], 0.02 * (i + 1), seed=i, aligned=False))
+    exp = [o.convert(f, n_threads=4) for f in frames]
+    with PreencodeSession(w, h, n_inflight=n, colorimetry=1, chroma_site=1) as s:
+        got = []
+        for base in range(0, len(frames), n):
+            ids = []
+            for k in range(n):
+                s.upload(k, frames[base + k])
+                ids.append(s.submit(k))
+            for fid in ids:
+                r = s.wait(fid)
+                got.append((r.frame.copy(), r.damage_map.copy(), r.damaged_count))
+    prev = None
+    for i, (fr, dm, cnt) in enumerate(got):
+        assert (fr == exp[i]).all(), i
+        em, en = o.damage(w, h, 0, exp[i], prev)
+        assert (dm == em).all() and cnt == en, i
+        prev = exp[i]
+
+
+def test_convert_only_mode():
+    f = rand_frame(640, 360, 8)
+    with PreencodeSession(640, 360, damage=False, colorimetry=0, chroma_site=0) as s:
+        r = s.convert(f)
+        assert r.damage_map is None
+    assert (r.frame == o.convert(f, matrix=0, chroma_site=0)).all()
+
+
+# ---- scale -----------------------------------------------------------------
+@pytest.mark.parametrize("dims", [(2560, 1440, 1920, 1080), (64, 48, 32, 24), (100, 60, 98, 34), (64, 48, 64, 24),
+                                  (64, 48, 30, 48), (64, 64, 16, 60), (1920, 1080, 1280, 720), (3840, 2160, 1920, 1080)])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_scale_parity(dims, variant):
+    w, h, ow, oh = dims
+    f0 = rand_frame(w, h, w + oh + variant)
+    f1 = synth.mutate(f0, 0.03, seed=variant, aligned=False)
+    for out_format, site in (("I420", 1), ("NV12", 0)):
+        check_sequence([f0, f1], w, h, out_w=ow, out_h=oh, variant=variant, out_format=out_format, chroma_site=site)
+
+
+def test_config3_desktop_content_bt709():
+    f0 = synth.desktop(2560, 1440)
+    f1 = synth.mutate(f0, 0.005, seed=1, aligned=False)
+    check_sequence([f0, f1, f1], 2560, 1440, out_w=1920, out_h=1080, out_format="I420", colorimetry="bt709")
+
+
+def test_enlarging_is_rejected():
+    with pytest.raises(PreencodeError) as e:
+        PreencodeSession(640, 360, out_width=1280, out_height=720)
+    assert e.value.code == _abi.SK_ERR_UNSUPPORTED
+
+
+# ---- device-resident and batched submission -------------------------------------
+def test_submit_device_and_alignment_check():
+    w, h = 1280, 720
+    f0, f1 = rand_frame(w, h, 1), rand_frame(w, h, 2)
+    with PreencodeSession(w, h, n_inflight=2, colorimetry=1, chroma_site=1) as s:
+        s.upload(0, f0); s.wait(s.submit(0))
+        s.upload(1, f1); s.wait(s.submit(1))
+        d0, st = s.device_input(0)
+        d1, _ = s.device_input(1)
+        before = launch_count()
+        r = s.wait(s.submit_device(d0, st))
+        assert launch_count() == before + 1
+        e0, e1 = o.convert(f0, n_threads=4), o.convert(f1, n_threads=4)
+        assert (r.frame == e0).all()
+        em, en = o.damage(w, h, 0, e0, e1)
+        assert (r.damage_map == em).all() and r.damaged_count == en
+        with pytest.raises(PreencodeError) as e:
+            s.submit_device(d1 + 4, st)
+        assert e.value.code == _abi.SK_ERR_ALIGN
+
+
+@pytest.mark.parametrize("fmt", ["NV12", "I420"])
+def test_batch_submit_matches_oracle_per_session(fmt):
+    w, h, n = 1920, 1080, 5
+    sessions = [PreencodeSession(w, h, out_format=fmt, colorimetry=1, chroma_site=1) for _ in range(n)]
+    try:
+        f0 = [rand_frame(w, h, 10 + i) for i in range(n)]
+        f1 = [synth.mutate(f, 0.01 * (i + 1), seed=i, aligned=False) for i, f in enumerate(f0)]
+        for s, a, b in zip(sessions, f0, f1):
+            s.upload(0, a); s.wait(s.submit(0))
+            s.upload(1, b); s.wait(s.submit(1))
+            s.reset_history()
+        ptr0 = [s.device_input(0)[0] for s in sessions]
+        ptr1 = [s.device_input(1)[0] for s in sessions]
+        stride = sessions[0].device_input(0)[1]
+        before = launch_count()
+        batch_submit(sessions, ptr0, stride, frame_id=100)
+        batch_submit(sessions, ptr1, stride, frame_id=101)
+        assert launch_count() == before + 2
+        ofmt = {"NV12": 0, "I420": 1}[fmt]
+        for i, s in enumerate(sessions):
+            e0 = o.convert(f0[i], out_fmt=ofmt, n_threads=4)
+            e1 = o.convert(f1[i], out_fmt=ofmt, n_threads=4)
+            r0 = s.wait(100)
+            assert (r0.frame == e0).all() and r0.damage_map.all()
+            r1 = s.wait(101)
+            em, en = o.damage(w, h, ofmt, e1, e0)
+            assert (r1.frame == e1).all() and (r1.damage_map == em).all() and r1.damaged_count == en
+    finally:
+        for s in sessions:
+            s.close()
+
+
+def test_batch_rejects_mixed_configuration():
+    a = PreencodeSession(640, 360)
+    b = PreencodeSession(640, 360, out_format="I420")
+    try:
+        a.upload(0, rand_frame(640, 360, 1)); a.wait(a.submit(0))
+        b.upload(0, rand_frame(640, 360, 2)); b.wait(b.submit(0))
+        with pytest.raises(PreencodeError) as e:
+            batch_submit([a, b], [a.device_input(0)[0], b.device_input(0)[0]], 0, 5)
+        assert e.value.code == _abi.SK_ERR_STATE
+    finally:
+        a.close(); b.close()
+
+
+def test_timing_fields_are_filled():
+    f = rand_frame(1920, 1080, 4)
+    with PreencodeSession(1920, 1080, timing=True) as s:
+        s.convert(f, 0)
+        r = s.convert(f, 1)
+        assert r.kernel_us > 0 and r.h2d_us > 0 and r.d2h_us > 0
+        assert s.last_kernel_us() == pytest.approx(r.kernel_us)
+
+
+def test_unknown_frame_id():
+    with PreencodeSession(64, 64) as s:
+        with pytest.raises(PreencodeError) as e:
+            s.wait(12345)
+        assert e.value.code == _abi.SK_ERR_STATE
+
+
+def test_linearity_property_on_luma_at_4k():
+    # size-independent property: adding k to G of every pixel raises the Y accumulator by 157k (BT.709), so
+    # Y changes by floor((acc+157k)/256)-floor(acc/256) ∈ {floor(157k/256), +1}; chroma of a grey ramp is 128/127.
+    w, h = 3840, 2160
+    f = np.zeros((h, w, 4), np.uint8)
+    ramp = (np.arange(w) % 200).astype(np.uint8)
+    f[..., 0] = f[..., 1] = f[..., 2] = ramp[None, :]
+    g = f.copy()
+    g[..., 1] += 32
+    with PreencodeSession(w, h, colorimetry=1, chroma_site=1, host_output=True) as s:
+        ya = s.planes(s.convert(f, 0).frame)[0].astype(int)
+        rb = s.convert(g, 1)
+        yb = s.planes(rb.frame)[0].astype(int)
+        d = yb - ya
+        assert d.min() >= (157 * 32) // 256 and d.max() <= (157 * 32) // 256 + 1
+        assert rb.damaged_count == 240 * 135
