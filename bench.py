@@ -73,7 +73,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except OSError:
@@ -199,22 +199,23 @@ def run_b200(args, rank, world, local_rank, dist):
     for s, (a, b) in zip(sess, inputs):
         s.upload(0, a); s.wait(s.submit(0))
         s.upload(1, b); s.wait(s.submit(1))
-    ptrs = [[s.device_input(k)[0] for s in sess] for k in (0, 1)]
+    batch = sk.SessionBatch(sess)
+    sets = [batch.frame_set([s.device_input(k)[0] for s in sess]) for k in (0, 1)]
     stride = sess[0].device_input(0)[1]
     leader = sess[0]
     fid = 1000
+    counts = []
 
     def step(k, wait_prev=True):
-        nonlocal fid
-        sk.batch_submit(sess, ptrs[k & 1], stride, fid)
+        nonlocal fid, counts
+        batch.submit(sets[k & 1], stride, fid)
         if wait_prev and fid > 1000:
-            for s in sess:
-                s.wait(fid - 1)
+            counts = batch.wait(fid - 1)      # the host consumes every session's damage count each step
         fid += 1
 
     def sync_all():
-        for s in sess:
-            s.wait(fid - 1)
+        nonlocal counts
+        counts = batch.wait(fid - 1)
 
     for k in range(args.warmup):
         step(k)
@@ -331,7 +332,7 @@ def run_b200(args, rank, world, local_rank, dist):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=3000)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sessions", type=int, default=16, help="4K sessions per GPU (one launch per step)")

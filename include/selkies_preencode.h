@@ -152,6 +152,10 @@ int sk_reset_history(sk_session *s);
 int sk_batch_submit(sk_session **sessions, int n, const void *const *dptrs,
                     size_t stride, uint64_t frame_id);
 
+/* Wait for frame_id on every session of a batch; damaged_counts (may be NULL)
+ * receives one exact count per session.  Maps stay readable through sk_wait. */
+int sk_batch_wait(sk_session **sessions, int n, uint64_t frame_id, uint32_t *damaged_counts);
+
 /* Device-side time of the last `sk_batch_submit`/`sk_submit*` kernel launch on
  * this session in microseconds (needs SK_FLAG_TIMING), for roofline accounting. */
 int sk_last_kernel_us(sk_session *s, float *us);

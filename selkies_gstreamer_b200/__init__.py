@@ -8,8 +8,8 @@ src/selkies/legacy/gstwebrtc_app.py:611 / :263-270 of the reference.
 """
 from . import _abi
 from ._abi import PreencodeLibraryError
-from .session import (FrameResult, PreencodeError, PreencodeSession, batch_submit, device_count,
+from .session import (FrameResult, PreencodeError, PreencodeSession, SessionBatch, batch_submit, device_count,
                       frame_layout, launch_count)
 
-__all__ = ["PreencodeSession", "PreencodeError", "PreencodeLibraryError", "FrameResult", "batch_submit",
+__all__ = ["PreencodeSession", "PreencodeError", "PreencodeLibraryError", "FrameResult", "SessionBatch", "batch_submit",
            "device_count", "frame_layout", "launch_count"]

@@ -29,7 +29,7 @@ SK_ABI_VERSION = 1
 EXPORTS = (
     "sk_session_create", "sk_session_destroy", "sk_get_input_staging", "sk_get_device_input",
     "sk_upload", "sk_submit", "sk_submit_device", "sk_wait", "sk_reset_history",
-    "sk_batch_submit", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
+    "sk_batch_submit", "sk_batch_wait", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
     "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
 )
 
@@ -110,6 +110,7 @@ def load() -> ctypes.CDLL:
         "sk_wait": (i, [vp, u64, ctypes.POINTER(SkResult)]),
         "sk_reset_history": (i, [vp]),
         "sk_batch_submit": (i, [vpp, i, vpp, sz, u64]),
+        "sk_batch_wait": (i, [vpp, i, u64, ctypes.POINTER(ctypes.c_uint32)]),
         "sk_last_kernel_us": (i, [vp, fp]),
         "sk_marker_record": (i, [vp, i]),
         "sk_marker_elapsed_us": (i, [vp, fp]),

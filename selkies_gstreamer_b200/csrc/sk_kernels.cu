@@ -131,9 +131,9 @@ __device__ __forceinline__ uint32_t chroma_v(uint32_t a0, uint32_t a1, uint32_t 
 // Block-level tail of the damage reduction: one atomic per CTA into the running
 // count, then a wrapping ticket; the last CTA of this frame publishes the total
 // and leaves both scratch words at zero for the next launch.
-__device__ __forceinline__ void finish_count(const SkFrame &f, uint32_t votes)
+__device__ __forceinline__ void finish_count(const SkFrame &f, uint32_t n)
 {
-    if (votes) atomicAdd(&f.scratch[0], (uint32_t)__popc(votes));
+    if (n) atomicAdd(&f.scratch[0], n);
     __threadfence();
     const uint32_t nblk = gridDim.x * gridDim.y;
     uint32_t t = atomicInc(&f.scratch[1], nblk - 1);
@@ -147,68 +147,76 @@ __device__ __forceinline__ void finish_count(const SkFrame &f, uint32_t votes)
 // CTA = 8 warps.  A warp covers 128*QX pixels of 2*RP rows; lane l owns the
 // quads at x = bx0 + q*128 + 4*l.  The CTA covers 16*RP rows = RP macroblock
 // rows, so a macroblock is 4 adjacent lanes of 8/RP adjacent warps.
-template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT>
-__global__ void __launch_bounds__(kThreads)
-sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+//
+// FULL = the CTA's whole footprint lies inside the frame: every access is an
+// unconditional, fully vectorised instruction.  Edge CTAs take the guarded path.
+template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT, bool FULL>
+__device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, const int bx0, const int y0,
+                                             const int lane, const bool have_prev,
+                                             uint32_t (&diff)[QX], int (&nvq)[QX])
 {
     constexpr int ROWS = 2 * RP;
-    const SkFrame &f = batch.f[blockIdx.z];
-    const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
-    const int bx0 = blockIdx.x * (128 * QX);
-    const int y0 = (blockIdx.y * 8 + warp) * ROWS;
     const int w = g.out_w, h = g.out_h;
-    const bool have_prev = DAMAGE && (f.prev != nullptr);
+    const int x0 = bx0 + lane * 4;
 
     uint4 px[ROWS][QX];
     uint32_t halo[ROWS];
     uint32_t py[ROWS][QX];
     uint32_t pc[RP][QX];
-    int nvq[QX];
+
+#pragma unroll
+    for (int q = 0; q < QX; q++) {
+        const int nv = w - (x0 + q * 128);
+        nvq[q] = FULL ? 4 : (nv >= 4 ? 4 : (nv > 0 ? 2 : 0));
+        diff[q] = 0;
+    }
+
+    // 32-bit byte offsets (largest frame: 8192*8192*4 B input, 100 MB output)
+    const uint32_t in_off = (uint32_t)y0 * (uint32_t)g.in_stride + 4u * (uint32_t)x0;
+    const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x0;
+    const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x0 : (uint32_t)(x0 >> 1));
+    const uint8_t *in = f.in + in_off;
+    const bool want_halo = SITE == 1 && lane == 0 && bx0 > 0;
 
     // ---- phase 1: issue every load of this thread up front
 #pragma unroll
-    for (int q = 0; q < QX; q++) {
-        int x = bx0 + q * 128 + lane * 4;
-        int nv = w - x;
-        nvq[q] = nv >= 4 ? 4 : (nv > 0 ? 2 : 0);
-    }
-#pragma unroll
     for (int r = 0; r < ROWS; r++) {
-        const bool rv = (y0 + r) < h;
-        const uint8_t *row = f.in + (size_t)(y0 + r) * g.in_stride;
+        const bool rv = FULL || (y0 + r) < h;
+        const uint8_t *row = in + (uint32_t)r * (uint32_t)g.in_stride;
 #pragma unroll
         for (int q = 0; q < QX; q++) {
-            int x = bx0 + q * 128 + lane * 4;
-            px[r][q] = load_quad<HINT>(row + 4 * (size_t)x, rv ? nvq[q] : 0);
+            if (FULL) px[r][q] = ld16<HINT>(row + q * 512);
+            else px[r][q] = load_quad<HINT>(row + q * 512, rv ? nvq[q] : 0);
         }
         halo[r] = 0;
-        if (SITE == 1 && lane == 0 && bx0 > 0 && rv)
-            halo[r] = ld4<0>(row + 4 * (size_t)(bx0 - 1));
+        if (want_halo && rv) halo[r] = ld4<0>(row - 4);   // lane 0: pixel left of the warp
     }
     if (DAMAGE) {
+        const uint8_t *pyb = f.prev + y_off;
 #pragma unroll
         for (int r = 0; r < ROWS; r++) {
-            const bool rv = have_prev && (y0 + r) < h;
+            const bool rv = have_prev && (FULL || (y0 + r) < h);
+            const uint8_t *row = pyb + (uint32_t)r * (uint32_t)g.y_stride;
 #pragma unroll
             for (int q = 0; q < QX; q++) {
-                int x = bx0 + q * 128 + lane * 4;
-                py[r][q] = load_word<HINT>(f.prev + (size_t)(y0 + r) * g.y_stride + x, rv ? nvq[q] : 0);
+                if (FULL) py[r][q] = rv ? ld4<HINT>(row + q * 128) : 0u;
+                else py[r][q] = load_word<HINT>(row + q * 128, rv ? nvq[q] : 0);
             }
         }
 #pragma unroll
         for (int rp = 0; rp < RP; rp++) {
-            const int yc = (y0 >> 1) + rp;
-            const bool rv = have_prev && (y0 + 2 * rp) < h;
+            const bool rv = have_prev && (FULL || (y0 + 2 * rp) < h);
+            const uint32_t o = c_off + (uint32_t)rp * (uint32_t)g.c_stride;
 #pragma unroll
             for (int q = 0; q < QX; q++) {
-                int x = bx0 + q * 128 + lane * 4;
-                int nv = rv ? nvq[q] : 0;
+                const int nv = rv ? nvq[q] : 0;
                 if (FMT == 0) {
-                    pc[rp][q] = load_word<HINT>(f.prev + g.off_c0 + (size_t)yc * g.c_stride + x, nv);
+                    const uint8_t *p = f.prev + g.off_c0 + o + q * 128;
+                    if (FULL) pc[rp][q] = rv ? ld4<HINT>(p) : 0u;
+                    else pc[rp][q] = load_word<HINT>(p, nv);
                 } else {
-                    const uint8_t *pu = f.prev + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
-                    const uint8_t *pv = f.prev + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+                    const uint8_t *pu = f.prev + g.off_c0 + o + q * 64;
+                    const uint8_t *pv = f.prev + g.off_c1 + o + q * 64;
                     uint32_t a = 0, b = 0;
                     if (nv == 4) { a = ld2<HINT>(pu); b = ld2<HINT>(pv); }
                     else if (nv == 2) { a = ld1(pu); b = ld1(pv); }
@@ -219,17 +227,14 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
     }
 
     // ---- phase 2: arithmetic, stores, compare
-    uint32_t diff[QX];
-#pragma unroll
-    for (int q = 0; q < QX; q++) diff[q] = 0;
-
+    uint8_t *oy = f.out + y_off;
 #pragma unroll
     for (int rp = 0; rp < RP; rp++) {
         uint32_t hh[2][QX][2];
 #pragma unroll
         for (int rr = 0; rr < 2; rr++) {
             const int r = 2 * rp + rr;
-            const bool rv = (y0 + r) < h;
+            const bool rv = FULL || (y0 + r) < h;
             uint32_t uvq[QX][4];
             uint32_t yw[QX];
 #pragma unroll
@@ -241,9 +246,10 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
                 uint32_t av = dp4a_us(halo[r], g.cv, 32768);
                 halo_uv = __byte_perm(au, av, 0x7531);
             }
+            uint8_t *orow = oy + (uint32_t)r * (uint32_t)g.y_stride;
 #pragma unroll
             for (int q = 0; q < QX; q++) {
-                const int x = bx0 + q * 128 + lane * 4;
+                const int x = x0 + q * 128;
                 uint32_t left = 0;
                 if (SITE == 1) {
                     left = __shfl_up_sync(kFull, uvq[q][3], 1);
@@ -251,26 +257,28 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
                     if (lane == 0) left = wrap;
                 }
                 chroma_h<SITE>(uvq[q], left, x, w, hh[rr][q][0], hh[rr][q][1]);
-                if (rv) store_word(f.out + (size_t)(y0 + r) * g.y_stride + x, yw[q], nvq[q]);
-                if (DAMAGE) {
-                    uint32_t m = nvq[q] == 4 ? 0xffffffffu : 0x0000ffffu;
-                    diff[q] |= (yw[q] ^ py[r][q]) & m;
+                if (FULL) *reinterpret_cast<uint32_t *>(orow + q * 128) = yw[q];
+                else if (rv) store_word(orow + q * 128, yw[q], nvq[q]);
+                if (DAMAGE && rv) {
+                    if (FULL) diff[q] |= yw[q] ^ py[r][q];
+                    else diff[q] |= (yw[q] ^ py[r][q]) & (nvq[q] == 4 ? 0xffffffffu : 0x0000ffffu);
                 }
             }
         }
-        const int yc = (y0 >> 1) + rp;
-        const bool rv = (y0 + 2 * rp) < h;
+        const bool rv = FULL || (y0 + 2 * rp) < h;
+        const uint32_t o = c_off + (uint32_t)rp * (uint32_t)g.c_stride;
 #pragma unroll
         for (int q = 0; q < QX; q++) {
-            const int x = bx0 + q * 128 + lane * 4;
             uint32_t cw = chroma_v<FMT>(hh[0][q][0], hh[0][q][1], hh[1][q][0], hh[1][q][1]);
             const int nv = rv ? nvq[q] : 0;
             if (FMT == 0) {
-                store_word(f.out + g.off_c0 + (size_t)yc * g.c_stride + x, cw, nv);
-                if (DAMAGE) diff[q] |= (cw ^ pc[rp][q]) & (nvq[q] == 4 ? 0xffffffffu : 0x0000ffffu);
+                uint8_t *p = f.out + g.off_c0 + o + q * 128;
+                if (FULL) *reinterpret_cast<uint32_t *>(p) = cw;
+                else store_word(p, cw, nv);
+                if (DAMAGE && rv) diff[q] |= (cw ^ pc[rp][q]) & ((FULL || nvq[q] == 4) ? 0xffffffffu : 0x0000ffffu);
             } else {
-                uint8_t *pu = f.out + g.off_c0 + (size_t)yc * g.c_stride + (x >> 1);
-                uint8_t *pv = f.out + g.off_c1 + (size_t)yc * g.c_stride + (x >> 1);
+                uint8_t *pu = f.out + g.off_c0 + o + q * 64;
+                uint8_t *pv = f.out + g.off_c1 + o + q * 64;
                 if (nv == 4) {
                     *reinterpret_cast<unsigned short *>(pu) = (unsigned short)cw;
                     *reinterpret_cast<unsigned short *>(pv) = (unsigned short)(cw >> 16);
@@ -278,15 +286,36 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
                     *pu = (uint8_t)cw;
                     *pv = (uint8_t)(cw >> 16);
                 }
-                if (DAMAGE) diff[q] |= (cw ^ pc[rp][q]) & (nvq[q] == 4 ? 0xffffffffu : 0x00ff00ffu);
+                if (DAMAGE && rv) diff[q] |= (cw ^ pc[rp][q]) & ((FULL || nvq[q] == 4) ? 0xffffffffu : 0x00ff00ffu);
             }
         }
     }
+}
+
+template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT>
+__global__ void __launch_bounds__(kThreads)
+sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+{
+    constexpr int ROWS = 2 * RP;
+    constexpr int NMB = RP * QX * 8;      // macroblocks per CTA
+    const SkFrame &f = batch.f[blockIdx.z];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int bx0 = blockIdx.x * (128 * QX);
+    const int by0 = blockIdx.y * (16 * RP);
+    const int y0 = by0 + warp * ROWS;
+    const bool have_prev = DAMAGE && (f.prev != nullptr);
+    const bool full = (bx0 + 128 * QX <= g.out_w) && (by0 + 16 * RP <= g.out_h);
+
+    uint32_t diff[QX];
+    int nvq[QX];
+    if (full) convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, true>(g, f, bx0, y0, lane, have_prev, diff, nvq);
+    else      convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, false>(g, f, bx0, y0, lane, have_prev, diff, nvq);
 
     // ---- phase 3: per-macroblock flags
     if (DAMAGE) {
         __shared__ uint32_t s_mask[8][QX];
-        const bool rows_valid = y0 < h;
+        const bool rows_valid = y0 < g.out_h;
 #pragma unroll
         for (int q = 0; q < QX; q++) {
             bool d = rows_valid && nvq[q] > 0 && (diff[q] != 0 || !have_prev);
@@ -294,27 +323,27 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
             if (lane == 0) s_mask[warp][q] = m;
         }
         __syncthreads();
-        if (warp == 0) {
-            constexpr int WPM = 8 / RP;                 // warps per macroblock row
-            bool flag = false, valid = false;
-            int bx = 0, by = 0;
-            if (lane < RP * QX * 8) {
-                const int mbrow = lane / (QX * 8);
-                const int q = (lane % (QX * 8)) / 8;
-                const int m = lane % 8;
-                uint32_t acc = 0;
+        constexpr int WPM = 8 / RP;                 // warps per macroblock row
+        bool hit = false;
+        if (threadIdx.x < NMB) {
+            const int t = threadIdx.x;
+            const int mbrow = t / (QX * 8);
+            const int q = (t % (QX * 8)) / 8;
+            const int m = t % 8;
+            uint32_t acc = 0;
 #pragma unroll
-                for (int k = 0; k < WPM; k++)
-                    acc |= s_mask[mbrow * WPM + k][q];
-                flag = ((acc >> (4 * m)) & 0xfu) != 0;
-                bx = blockIdx.x * (8 * QX) + q * 8 + m;
-                by = blockIdx.y * RP + mbrow;
-                valid = bx < g.mb_w && by < g.mb_h;
-                if (valid) f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+            for (int k = 0; k < WPM; k++)
+                acc |= s_mask[mbrow * WPM + k][q];
+            const bool flag = ((acc >> (4 * m)) & 0xfu) != 0;
+            const int bx = blockIdx.x * (8 * QX) + q * 8 + m;
+            const int by = blockIdx.y * RP + mbrow;
+            if (bx < g.mb_w && by < g.mb_h) {
+                f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                hit = flag;
             }
-            uint32_t votes = __ballot_sync(kFull, valid && flag);
-            if (lane == 0) finish_count(f, votes);
         }
+        const int total = __syncthreads_count(hit);
+        if (threadIdx.x == 0) finish_count(f, (uint32_t)total);
     }
 }
 
@@ -464,7 +493,7 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
                 if (valid) f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
             }
             uint32_t votes = __ballot_sync(kFull, valid && flag);
-            if (lane == 0) finish_count(f, votes);
+            if (lane == 0) finish_count(f, (uint32_t)__popc(votes));
         }
     }
 }
@@ -489,9 +518,11 @@ cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaS
 
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant)
 {
+    // variant 0 = library default, chosen by the sweep in profiles/ (RP=1, QX=2, plain __ldg)
     switch (variant) {
     default:
-    case 0: return launch_convert_shape<1, 1, 0>(g, b, n, st);
+    case 0: return launch_convert_shape<1, 2, 0>(g, b, n, st);
+    case 15: return launch_convert_shape<1, 1, 0>(g, b, n, st);
     case 1: return launch_convert_shape<2, 1, 0>(g, b, n, st);
     case 2: return launch_convert_shape<1, 2, 0>(g, b, n, st);
     case 3: return launch_convert_shape<2, 2, 0>(g, b, n, st);
@@ -499,6 +530,12 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
     case 5: return launch_convert_shape<2, 1, 1>(g, b, n, st);
     case 6: return launch_convert_shape<1, 2, 1>(g, b, n, st);
     case 7: return launch_convert_shape<2, 2, 1>(g, b, n, st);
+    case 8: return launch_convert_shape<4, 1, 0>(g, b, n, st);
+    case 9: return launch_convert_shape<4, 2, 0>(g, b, n, st);
+    case 10: return launch_convert_shape<2, 4, 0>(g, b, n, st);
+    case 11: return launch_convert_shape<1, 4, 0>(g, b, n, st);
+    case 12: return launch_convert_shape<4, 2, 1>(g, b, n, st);
+    case 13: return launch_convert_shape<2, 4, 1>(g, b, n, st);
     }
 }
 

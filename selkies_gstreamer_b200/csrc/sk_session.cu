@@ -548,10 +548,14 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
     g.in_stride = (int)stride;
     SkBatch b;
     int ris[SK_MAX_BATCH];
+    cudaEvent_t waited = nullptr;      // members of a steady batch share one event: wait on it once
     for (int i = 0; i < n; i++) {
         sk_session *s = ss[i];
         Ring &r = s->ring[s->seq % (uint64_t)s->n];
-        if (r.used) SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, r.wait_on, 0));
+        if (r.used && r.wait_on != waited) {
+            SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, r.wait_on, 0));
+            waited = r.wait_on;
+        }
         if (s->last_kernel_stream && s->last_kernel_stream != L->s_comp)
             SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, s->last_kernel_event, 0));
         r.had_h2d = false;
@@ -625,6 +629,22 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
             if (cudaEventElapsedTime(&ms, r.d2h_start, r.done) == cudaSuccess) out->d2h_us = ms * 1e3f;
             cudaGetLastError();
         }
+    }
+    return SK_OK;
+}
+
+int sk_batch_wait(sk_session **ss, int n, uint64_t frame_id, uint32_t *damaged_counts)
+{
+    if (!ss || n < 1 || !ss[0]) return SK_ERR_ARG;
+    for (int i = 0; i < n; i++) {
+        if (!ss[i]) return fail(ss[0], SK_ERR_ARG, "null session in batch");
+        sk_result r;
+        int rc = sk_wait(ss[i], frame_id, &r);
+        if (rc != SK_OK) {
+            if (i > 0) ss[0]->err = ss[i]->err;
+            return rc;
+        }
+        if (damaged_counts) damaged_counts[i] = r.damaged_count;
     }
     return SK_OK;
 }

@@ -152,6 +152,9 @@ class PreencodeSession:
         return int(frame_id)
 
     def wait(self, frame_id: int) -> FrameResult:
+        """Block until `frame_id` is done. `frame` and `damage_map` are BORROWED views of the
+        library's pinned buffers: valid until n_inflight more frames are submitted or the
+        session is closed — copy them if they must outlive that."""
         r = _abi.SkResult()
         self._check(self._lib.sk_wait(self._h, frame_id, ctypes.byref(r)))
         frame = dmap = None
@@ -164,10 +167,14 @@ class PreencodeSession:
         return FrameResult(r.frame_id, frame, dmap, r.damaged_count, r.dev_frame or 0, r.dev_damage_map or 0,
                            tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us)
 
-    def convert(self, frame: np.ndarray, slot: int = 0) -> FrameResult:
-        """Synchronous convenience: upload → submit → wait."""
+    def convert(self, frame: np.ndarray, slot: int = 0, copy: bool = False) -> FrameResult:
+        """Synchronous convenience: upload → submit → wait (see wait() about borrowed views)."""
         self.upload(slot, frame)
-        return self.wait(self.submit(slot))
+        r = self.wait(self.submit(slot))
+        if copy:
+            r.frame = None if r.frame is None else r.frame.copy()
+            r.damage_map = None if r.damage_map is None else r.damage_map.copy()
+        return r
 
     def reset_history(self):
         self._check(self._lib.sk_reset_history(self._h))
@@ -213,6 +220,41 @@ def batch_submit(sessions: list[PreencodeSession], dptrs: list[int], stride: int
     for s in sessions:
         s._next_id = frame_id + 1
     return frame_id
+
+
+class SessionBatch:
+    """A fixed group of same-configuration sessions on one GPU, submitted with one launch per
+    frame (throughput mode: many desktops per GPU).  ctypes arrays are built once."""
+
+    def __init__(self, sessions: list[PreencodeSession]):
+        if not sessions:
+            raise ValueError("empty batch")
+        if len(sessions) > _abi.SK_MAX_BATCH:
+            raise ValueError(f"at most {_abi.SK_MAX_BATCH} sessions per batch")
+        self.sessions = list(sessions)
+        self._lib = sessions[0]._lib
+        self._n = len(sessions)
+        self._handles = (ctypes.c_void_p * self._n)(*[s._h.value for s in sessions])
+        self._counts = (ctypes.c_uint32 * self._n)()
+        self._frames = {}
+
+    def frame_set(self, dptrs: list[int]):
+        """Pre-build the pointer array for one set of resident frames (one per session)."""
+        if len(dptrs) != self._n:
+            raise ValueError("one device pointer per session")
+        return (ctypes.c_void_p * self._n)(*dptrs)
+
+    def submit(self, frame_set, stride: int, frame_id: int) -> int:
+        rc = self._lib.sk_batch_submit(self._handles, self._n, frame_set, stride, frame_id)
+        if rc != _abi.SK_OK:
+            raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
+        return frame_id
+
+    def wait(self, frame_id: int) -> list[int]:
+        rc = self._lib.sk_batch_wait(self._handles, self._n, frame_id, self._counts)
+        if rc != _abi.SK_OK:
+            raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
+        return list(self._counts)
 
 
 def launch_count() -> int:

@@ -1,0 +1,425 @@
+"""Element logic without GStreamer: properties, caps negotiation, per-frame transform.
+
+This is the host-side mirror of the element contract the reference relies on
+when it instantiates and links the stock stage
+(src/selkies/legacy/gstwebrtc_app.py:611-617 videoconvert, :263-284
+cudaupload+cudaconvert, :941-994 add/link):
+
+  * GObject properties it sets: `n-threads` (:612), `qos` (:613, :277),
+    `cuda-device-id` (:264-272); videoscale's `method` / `add-borders` for the
+    scale capability the stage also covers.
+  * caps: sink video/x-raw {BGRx,BGRA,RGBx,RGBA}; src video/x-raw {NV12,I420},
+    format forced by the downstream capsfilter (:614-617).
+  * GstBaseTransform vmethods: transform_caps / fixate_caps / set_caps /
+    get_unit_size / start / stop / transform.
+
+`gst_element.py` adapts this class to a real GstBase.BaseTransform; keeping the
+logic here lets it be tested where `gi` does not exist.  Pixel work is never
+done here: transform() hands pointers to libselkies_preencode.so.
+"""
+from __future__ import annotations
+
+import ctypes
+import re
+import threading
+from fractions import Fraction
+
+from . import _abi, colorimetry as _col
+from .session import PreencodeError, PreencodeSession, frame_layout
+
+SINK_FORMATS = ("BGRx", "BGRA", "RGBx", "RGBA")
+SRC_FORMATS = ("NV12", "I420")
+MIN_DIM, MAX_DIM = 2, 8192           # reference caps the display at 7680x4320 (resize.py:66)
+
+FLOW_OK, FLOW_NOT_NEGOTIATED, FLOW_ERROR = 0, -4, -5      # Gst.FlowReturn values
+SINK, SRC = "sink", "src"
+
+SINK_TEMPLATE = ("video/x-raw, format=(string){ BGRx, BGRA, RGBx, RGBA }, "
+                 "width=(int)[ 2, 8192 ], height=(int)[ 2, 8192 ], framerate=(fraction)[ 0/1, 2147483647/1 ]")
+SRC_TEMPLATE = ("video/x-raw, format=(string){ NV12, I420 }, "
+                "width=(int)[ 2, 8192 ], height=(int)[ 2, 8192 ], framerate=(fraction)[ 0/1, 2147483647/1 ]")
+
+
+class IntRange(tuple):
+    """[lo, hi] inclusive."""
+    def __new__(cls, lo, hi):
+        return super().__new__(cls, (int(lo), int(hi)))
+
+
+# ----------------------------------------------------------------- caps (subset of GstCaps syntax)
+def parse_caps(text: str) -> list[dict]:
+    """Parse the subset of Gst.Caps.to_string() this stage negotiates with."""
+    out = []
+    for part in _split_top(text, ";"):
+        part = part.strip()
+        if not part:
+            continue
+        fields = _split_top(part, ",")
+        name = fields[0].strip()
+        feat = None
+        m = re.match(r"^([^()]+)\((.+)\)$", name)
+        if m:
+            name, feat = m.group(1).strip(), m.group(2).strip()
+        st = {"name": name}
+        if feat:
+            st["features"] = feat
+        for f in fields[1:]:
+            if "=" not in f:
+                continue
+            k, v = f.split("=", 1)
+            st[k.strip()] = _parse_value(v.strip())
+        out.append(st)
+    return out
+
+
+def _split_top(s: str, sep: str) -> list[str]:
+    parts, depth, cur = [], 0, []
+    for ch in s:
+        if ch in "{[(<":
+            depth += 1
+        elif ch in "}])>":
+            depth -= 1
+        if ch == sep and depth == 0:
+            parts.append("".join(cur)); cur = []
+        else:
+            cur.append(ch)
+    parts.append("".join(cur))
+    return parts
+
+
+def _parse_scalar(v: str):
+    v = v.strip().strip('"')
+    if re.fullmatch(r"-?\d+", v):
+        return int(v)
+    if re.fullmatch(r"-?\d+/\d+", v):
+        return Fraction(v)
+    return v
+
+
+def _parse_value(v: str):
+    v = re.sub(r"^\(\w+\)\s*", "", v)
+    if v.startswith("{"):
+        return [_parse_scalar(x) for x in _split_top(v[1:-1], ",")]
+    if v.startswith("["):
+        lo, hi = [_parse_scalar(x) for x in _split_top(v[1:-1], ",")][:2]
+        if isinstance(lo, int) and isinstance(hi, int):
+            return IntRange(lo, hi)
+        return (lo, hi)
+    return _parse_scalar(v)
+
+
+def caps_to_string(caps: list[dict]) -> str:
+    def val(v):
+        if isinstance(v, IntRange):
+            return f"(int)[ {v[0]}, {v[1]} ]"
+        if isinstance(v, tuple):
+            return f"(fraction)[ {v[0]}, {v[1]} ]" if isinstance(v[0], Fraction) else f"[ {v[0]}, {v[1]} ]"
+        if isinstance(v, list):
+            return "{ " + ", ".join(str(x) for x in v) + " }"
+        if isinstance(v, Fraction):
+            return f"(fraction){v.numerator}/{v.denominator}"
+        if isinstance(v, int):
+            return f"(int){v}"
+        return f"(string){v}"
+    out = []
+    for st in caps:
+        name = st["name"] + (f"({st['features']})" if st.get("features") else "")
+        out.append(", ".join([name] + [f"{k}={val(v)}" for k, v in st.items() if k not in ("name", "features")]))
+    return "; ".join(out)
+
+
+def _as_list(v):
+    return v if isinstance(v, list) else [v]
+
+
+def _intersect_value(a, b):
+    """Intersection of two field values (scalar / list / IntRange); None if empty."""
+    if isinstance(a, IntRange) and isinstance(b, IntRange):
+        lo, hi = max(a[0], b[0]), min(a[1], b[1])
+        return None if lo > hi else (lo if lo == hi else IntRange(lo, hi))
+    if isinstance(a, IntRange) or isinstance(b, IntRange):
+        rng, other = (a, b) if isinstance(a, IntRange) else (b, a)
+        keep = [x for x in _as_list(other) if isinstance(x, int) and rng[0] <= x <= rng[1]]
+        return None if not keep else (keep[0] if len(keep) == 1 else keep)
+    if isinstance(a, tuple) or isinstance(b, tuple):      # fraction ranges: accept the other side
+        return b if isinstance(a, tuple) else a
+    keep = [x for x in _as_list(a) if x in _as_list(b)]
+    return None if not keep else (keep[0] if len(keep) == 1 else keep)
+
+
+def intersect_caps(a: list[dict], b: list[dict]) -> list[dict]:
+    out = []
+    for sa in a:
+        for sb in b:
+            if sa["name"] != sb["name"] or sa.get("features") != sb.get("features"):
+                continue
+            st, ok = {"name": sa["name"]}, True
+            if sa.get("features"):
+                st["features"] = sa["features"]
+            for k in list(sa.keys()) + [k for k in sb if k not in sa]:
+                if k in ("name", "features"):
+                    continue
+                if k in sa and k in sb:
+                    v = _intersect_value(sa[k], sb[k])
+                    if v is None:
+                        ok = False
+                        break
+                    st[k] = v
+                else:
+                    st[k] = sa.get(k, sb.get(k))
+            if ok:
+                out.append(st)
+    return out
+
+
+def is_fixed(st: dict) -> bool:
+    return all(not isinstance(v, (list, tuple)) for k, v in st.items())
+
+
+# ----------------------------------------------------------------- the stage
+class StageError(RuntimeError):
+    pass
+
+
+class PreEncodeStage:
+    """One convert[+scale]+damage stage instance (what one videoconvert element is)."""
+
+    PROPERTIES = {
+        # name: (type, default, validator)
+        "qos": (bool, True, None),                                   # gstwebrtc_app.py:613 / :277
+        "n-threads": (int, 1, lambda v: 0 <= v <= 0xFFFFFFFF),       # gstwebrtc_app.py:612 (accepted; the GPU path has no CPU threads)
+        "cuda-device-id": (int, -1, lambda v: v >= -1),              # gstwebrtc_app.py:264-272
+        "method": (str, "bilinear", lambda v: v in ("bilinear", 1)),  # videoscale method; only bilinear
+        "add-borders": (bool, False, lambda v: v is False),
+        "damage": (bool, True, None),
+        "n-inflight": (int, 2, lambda v: 2 <= v <= 8),
+        "scale-variant": (int, _abi.SK_SCALE_VARIANT_GST_LQ, lambda v: v in (0, 1)),
+    }
+    READ_ONLY = ("frames", "damaged-blocks", "damaged-fraction", "total-blocks")
+
+    def __init__(self, name: str = "b200preencode0"):
+        self.name = name
+        self._props = {k: d for k, (_, d, _) in self.PROPERTIES.items()}
+        self._lock = threading.Lock()       # set_caps may come from another thread than transform (§8b)
+        self._session: PreencodeSession | None = None
+        self._in = self._out = None
+        self._started = False
+        self.frames = 0
+        self.last_damage_map = None
+        self.last_damaged = 0
+        self.last_error = ""
+        self.on_damage = None               # callable(stage, map, count): hook for ROI / keyframe policy
+
+    # -- properties ---------------------------------------------------------
+    def set_property(self, name: str, value):
+        if name in self.READ_ONLY:
+            raise StageError(f"property '{name}' of '{self.name}' is not writable")
+        if name not in self.PROPERTIES:
+            raise StageError(f"object class 'B200PreEncode' has no property named '{name}'")
+        typ, _, check = self.PROPERTIES[name]
+        if typ is bool:
+            if not isinstance(value, (bool, int)):
+                raise StageError(f"property '{name}' expects a boolean")
+            value = bool(value)
+        elif typ is int:
+            if isinstance(value, bool) or not isinstance(value, int):
+                raise StageError(f"property '{name}' expects an integer")
+        if name == "method" and value == 1:
+            value = "bilinear"
+        if check and not check(value):
+            raise StageError(f"value {value!r} out of range for property '{name}'")
+        with self._lock:
+            changed = self._props[name] != value
+            self._props[name] = value
+            needs_session = name in ("cuda-device-id", "damage", "n-inflight", "scale-variant")
+            if changed and needs_session and self._session is not None:
+                self._recreate_locked()
+
+    def get_property(self, name: str):
+        if name == "frames":
+            return self.frames
+        if name == "damaged-blocks":
+            return self.last_damaged
+        if name == "total-blocks":
+            return 0 if not self._out else ((self._out["width"] + 15) // 16) * ((self._out["height"] + 15) // 16)
+        if name == "damaged-fraction":
+            t = self.get_property("total-blocks")
+            return (self.last_damaged / t) if t else 0.0
+        if name not in self._props:
+            raise StageError(f"object class 'B200PreEncode' has no property named '{name}'")
+        return self._props[name]
+
+    # -- negotiation ----------------------------------------------------------
+    @staticmethod
+    def template(direction: str) -> list[dict]:
+        return parse_caps(SINK_TEMPLATE if direction == SINK else SRC_TEMPLATE)
+
+    def transform_caps(self, direction: str, caps: list[dict], filter_caps: list[dict] | None = None) -> list[dict]:
+        """Caps possible on the OTHER pad given `caps` on the `direction` pad.
+
+        Format becomes every format of the other side, size becomes the range this
+        stage can produce/accept (it shrinks, never enlarges), colorimetry and
+        chroma-site do not carry across an RGB↔YUV change; everything else
+        (framerate, pixel-aspect-ratio, ...) is kept."""
+        out = []
+        other_formats = list(SRC_FORMATS if direction == SINK else SINK_FORMATS)
+        for st in caps:
+            if st.get("name") != "video/x-raw" or st.get("features") not in (None, "memory:SystemMemory"):
+                continue
+            o = {k: v for k, v in st.items() if k not in ("format", "colorimetry", "chroma-site", "width", "height")}
+            o["format"] = other_formats
+            for dim in ("width", "height"):
+                v = st.get(dim, IntRange(MIN_DIM, MAX_DIM))
+                if isinstance(v, int):
+                    o[dim] = IntRange(MIN_DIM, v) if direction == SINK else IntRange(v, MAX_DIM)
+                elif isinstance(v, IntRange):
+                    o[dim] = IntRange(MIN_DIM, v[1]) if direction == SINK else IntRange(v[0], MAX_DIM)
+                else:
+                    o[dim] = IntRange(MIN_DIM, MAX_DIM)
+            out.append(o)
+        out = intersect_caps(out, self.template(SRC if direction == SINK else SINK))
+        if filter_caps is not None:
+            out = intersect_caps(filter_caps, out)
+        return out
+
+    def fixate_caps(self, direction: str, caps: list[dict], othercaps: list[dict]) -> dict:
+        """Pick one structure of `othercaps`: same size as the input if allowed, else the
+        nearest allowed size; first listed format; framerate of the input."""
+        if not othercaps:
+            raise StageError("not negotiated: empty caps")
+        src = caps[0]
+        st = dict(othercaps[0])
+        for dim in ("width", "height"):
+            want = src.get(dim)
+            v = st.get(dim)
+            if isinstance(v, IntRange):
+                pick = want if isinstance(want, int) else v[1]
+                pick = min(max(pick, v[0]), v[1])
+                st[dim] = pick & ~1 if pick > 1 else pick
+            elif isinstance(v, list):
+                st[dim] = min(v, key=lambda x: abs(x - (want if isinstance(want, int) else x)))
+        if isinstance(st.get("format"), list):
+            st["format"] = st["format"][0]
+        fr = st.get("framerate")
+        if isinstance(fr, (tuple, list)):
+            st["framerate"] = src.get("framerate") if isinstance(src.get("framerate"), Fraction) else Fraction(60, 1)
+        for k, v in list(st.items()):
+            if isinstance(v, list):
+                st[k] = v[0]
+        return st
+
+    @staticmethod
+    def get_unit_size(caps: dict) -> int:
+        """Bytes of one frame of fixed caps (GstVideoInfo default layout)."""
+        w, h, fmt = caps["width"], caps["height"], caps["format"]
+        if fmt in SINK_FORMATS:
+            return 4 * w * h
+        if fmt in SRC_FORMATS:
+            return frame_layout(w, h, fmt)[0]
+        raise StageError(f"unsupported format {fmt}")
+
+    def start(self) -> bool:
+        self._started = True
+        return True
+
+    def stop(self) -> bool:
+        with self._lock:
+            if self._session is not None:
+                self._session.close()
+                self._session = None
+            self._started = False
+        return True
+
+    def set_caps(self, incaps: dict, outcaps: dict) -> bool:
+        """(Re)create the GPU session for fixed caps; the next frame has no predecessor."""
+        try:
+            for c in (incaps, outcaps):
+                if not is_fixed(c):
+                    raise StageError("caps are not fixed")
+            if incaps["format"] not in SINK_FORMATS or outcaps["format"] not in SRC_FORMATS:
+                raise StageError(f"cannot convert {incaps['format']} to {outcaps['format']}")
+            for c in (incaps, outcaps):
+                if c["width"] % 2 or c["height"] % 2:
+                    raise StageError("width and height must be even (the reference forces even sizes: "
+                                     "webrtc_input.py:677, resize.py:28)")
+            with self._lock:
+                same = (self._in is not None and self._session is not None and
+                        all(self._in.get(k) == incaps.get(k) for k in ("format", "width", "height")) and
+                        all(self._out.get(k) == outcaps.get(k) for k in
+                            ("format", "width", "height", "colorimetry", "chroma-site")))
+                self._in, self._out = dict(incaps), dict(outcaps)
+                if same:
+                    return True          # e.g. framerate-only renegotiation (set_framerate, gstwebrtc_app.py:1264-1266)
+                self._recreate_locked()
+            return True
+        except (StageError, PreencodeError, ValueError, KeyError) as e:
+            self.last_error = str(e)
+            return False
+
+    def _recreate_locked(self):
+        if self._session is not None:
+            self._session.close()
+            self._session = None
+        i, o = self._in, self._out
+        self._session = PreencodeSession(
+            i["width"], i["height"], in_format=i["format"], out_format=o["format"],
+            out_width=o["width"], out_height=o["height"], colorimetry=o.get("colorimetry"),
+            chroma_site=o.get("chroma-site"), device_id=self._props["cuda-device-id"],
+            n_inflight=self._props["n-inflight"], damage=self._props["damage"], host_output=True,
+            scale_variant=self._props["scale-variant"])
+        self.frames = 0
+
+    @property
+    def session(self) -> PreencodeSession | None:
+        return self._session
+
+    def src_caps_fields(self) -> dict:
+        """colorimetry / chroma-site actually used (what the src caps should advertise)."""
+        s = self._session
+        return {} if s is None else {"colorimetry": _col.MATRIX_NAMES[s.matrix], "chroma-site": _col.SITE_NAMES[s.site]}
+
+    # -- per frame --------------------------------------------------------------
+    def transform(self, in_ptr: int, in_size: int, out_ptr: int, out_size: int, in_stride: int = 0) -> int:
+        """One frame: raw host pointers in, raw host pointers out. Returns a FlowReturn value."""
+        with self._lock:
+            s = self._session
+            if s is None:
+                self.last_error = "not negotiated"
+                return FLOW_NOT_NEGOTIATED
+            try:
+                stride = in_stride or 4 * s.width
+                if in_size < stride * (s.height - 1) + 4 * s.width:
+                    raise StageError(f"input buffer too small: {in_size} bytes")
+                if out_size < s.frame_bytes:
+                    raise StageError(f"output buffer too small: {out_size} < {s.frame_bytes}")
+                slot = self.frames % s.n_inflight
+                s._check(s._lib.sk_upload(s.handle, slot, ctypes.c_void_p(in_ptr), stride))
+                r = s.wait(s.submit(slot))
+                ctypes.memmove(out_ptr, r.frame.ctypes.data, s.frame_bytes)
+                self.frames += 1
+                self.last_damage_map = r.damage_map
+                self.last_damaged = r.damaged_count
+                if self.on_damage is not None and r.damage_map is not None:
+                    self.on_damage(self, r.damage_map, r.damaged_count)
+                return FLOW_OK
+            except (StageError, PreencodeError) as e:
+                self.last_error = str(e)
+                return FLOW_ERROR
+
+    def transform_array(self, frame):
+        """numpy convenience around transform(): returns (packed output, damage map, count)."""
+        import numpy as np
+        s = self._session
+        if s is None:
+            raise StageError("not negotiated")
+        frame = np.ascontiguousarray(frame)
+        out = np.empty(s.frame_bytes, np.uint8)
+        rc = self.transform(frame.ctypes.data, frame.nbytes, out.ctypes.data, out.nbytes)
+        if rc != FLOW_OK:
+            raise StageError(self.last_error)
+        return out, (None if self.last_damage_map is None else self.last_damage_map.copy()), self.last_damaged
+
+    def reset_history(self):
+        with self._lock:
+            if self._session is not None:
+                self._session.reset_history()

@@ -24,7 +24,8 @@ def oracle_frame(frame, sess_kw, out_w=None, out_h=None, variant=0):
     return o.convert(frame, out_w, out_h,
                      in_fmt={"BGRx": 0, "RGBx": 1, "BGRA": 0, "RGBA": 1}[sess_kw.get("in_format", "BGRx")],
                      out_fmt={"NV12": 0, "I420": 1}[sess_kw.get("out_format", "NV12")],
-                     matrix=sess_kw["colorimetry"], chroma_site=sess_kw["chroma_site"],
+                     matrix={"bt601": 0, "bt709": 1, "bt2020": 2}.get(sess_kw["colorimetry"], sess_kw["colorimetry"]),
+                     chroma_site=sess_kw["chroma_site"],
                      scale_variant=variant, n_threads=8)
 
 
@@ -99,7 +100,7 @@ def test_small_and_ragged_sizes_all_modes(w, h):
                                in_format=in_format)
 
 
-@pytest.mark.parametrize("variant", range(8))
+@pytest.mark.parametrize("variant", range(16))
 def test_every_kernel_variant_is_bit_exact(variant):
     lib = _abi.load()
     try:
@@ -130,7 +131,7 @@ def test_default_colorimetry_by_height():
         with PreencodeSession(w, h) as s:
             assert (s.matrix, s.site) == (m, site)
             r = s.convert(f)
-        assert (r.frame == o.convert(f, matrix=m, chroma_site=site, n_threads=8)).all()
+            assert (r.frame == o.convert(f, matrix=m, chroma_site=site, n_threads=8)).all()
 
 
 def test_bars_and_checkerboard_exercise_chroma_filters():
@@ -144,6 +145,7 @@ def test_padding_byte_does_not_matter():
     g = f.copy()
     g[..., 3] = 0
     with PreencodeSession(256, 64) as s:
+        assert (s.matrix, s.site) == (0, 0)      # SD default: bt601, chroma-site none
         a = s.convert(f, 0)
         fa = a.frame.copy()
         b = s.convert(g, 1)
@@ -159,7 +161,7 @@ def test_strided_capture_rows():
         assert st.shape == (64, 4 * 256 + 40)
         s.upload(0, view)
         r = s.wait(s.submit(0))
-    assert (r.frame == o.convert(np.ascontiguousarray(view), n_threads=2)).all()
+        assert (r.frame == o.convert(np.ascontiguousarray(view), matrix=s.matrix, chroma_site=s.site, n_threads=2)).all()
 
 
 def test_idempotence_and_reset_history():
@@ -205,7 +207,7 @@ def test_convert_only_mode():
     with PreencodeSession(640, 360, damage=False, colorimetry=0, chroma_site=0) as s:
         r = s.convert(f)
         assert r.damage_map is None
-    assert (r.frame == o.convert(f, matrix=0, chroma_site=0)).all()
+        assert (r.frame == o.convert(f, matrix=0, chroma_site=0)).all()
 
 
 # ---- scale -----------------------------------------------------------------
