@@ -1,0 +1,209 @@
+"""GstBase.BaseTransform adaptor: the drop-in for `videoconvert` / `cudaupload ! cudaconvert`
+in the pipeline the reference builds (src/selkies/legacy/gstwebrtc_app.py:611-617, :263-284).
+
+All logic lives in stage.PreEncodeStage; this file only translates between GStreamer
+objects and it.  `gi` is imported lazily because it does not exist where the kernels are
+developed and benchmarked; the reference itself subclasses a GObject type with do_*
+vmethods in Python (PlayoutDelayExtension, gstwebrtc_app.py:1744-1780), which is the
+precedent for registering an in-process Python element with Gst.Element.register.
+
+    from selkies_gstreamer_b200 import gst_element
+    gst_element.register()                      # after Gst.init()
+    conv = Gst.ElementFactory.make("b200preencode")
+"""
+from __future__ import annotations
+
+import ctypes
+
+from . import stage as _stage
+
+FACTORY_NAME = "b200preencode"
+_element_class = None
+
+
+class _MapError(RuntimeError):
+    pass
+
+
+class _GstMapInfo(ctypes.Structure):      # gstmemory.h: GstMapInfo
+    _fields_ = [("memory", ctypes.c_void_p), ("flags", ctypes.c_int), ("data", ctypes.c_void_p),
+                ("size", ctypes.c_size_t), ("maxsize", ctypes.c_size_t),
+                ("user_data", ctypes.c_void_p * 4), ("_gst_reserved", ctypes.c_void_p * 4)]
+
+
+_libgst = False
+
+
+def _raw_gst():
+    """libgstreamer through ctypes: PyGObject's Buffer.map() hands back *copies*, which would cost a
+    33 MB Python-side memcpy per 4K frame; gst_buffer_map on the boxed pointer does not."""
+    global _libgst
+    if _libgst is False:
+        try:
+            lib = ctypes.CDLL("libgstreamer-1.0.so.0")
+            lib.gst_buffer_map.argtypes = [ctypes.c_void_p, ctypes.POINTER(_GstMapInfo), ctypes.c_int]
+            lib.gst_buffer_map.restype = ctypes.c_int
+            lib.gst_buffer_unmap.argtypes = [ctypes.c_void_p, ctypes.POINTER(_GstMapInfo)]
+            lib.gst_buffer_unmap.restype = None
+            _libgst = lib
+        except OSError:
+            _libgst = None
+    return _libgst
+
+
+class _mapped:
+    """Context manager giving (ptr, size) of a Gst.Buffer. Zero-copy through libgstreamer when it can
+    be loaded; otherwise PyGObject's copying map, with the output written back by Buffer.fill()."""
+
+    def __init__(self, Gst, buf, write: bool):
+        self.Gst, self.buf, self.write = Gst, buf, write
+        self.ptr = self.size = 0
+        self._info = self._tmp = self._pymap = None
+
+    def __enter__(self):
+        lib = _raw_gst()
+        if lib is not None:
+            self._info = _GstMapInfo()
+            flags = 2 if self.write else 1            # GST_MAP_WRITE / GST_MAP_READ
+            if not lib.gst_buffer_map(hash(self.buf), ctypes.byref(self._info), flags):
+                self._info = None
+                raise _MapError("gst_buffer_map failed")
+            self.ptr, self.size = self._info.data, self._info.size
+            return self
+        if self.write:
+            self.size = self.buf.get_size()
+            self._tmp = (ctypes.c_uint8 * self.size)()
+        else:
+            ok, self._pymap = self.buf.map(self.Gst.MapFlags.READ)
+            if not ok:
+                raise _MapError("Gst.Buffer.map failed")
+            self.size = self._pymap.size
+            self._tmp = (ctypes.c_uint8 * self.size).from_buffer_copy(self._pymap.data)
+        self.ptr = ctypes.addressof(self._tmp)
+        return self
+
+    def __exit__(self, et, ev, tb):
+        if self._info is not None:
+            _raw_gst().gst_buffer_unmap(hash(self.buf), ctypes.byref(self._info))
+        elif self.write:
+            if et is None:
+                self.buf.fill(0, bytes(self._tmp))
+        elif self._pymap is not None:
+            self.buf.unmap(self._pymap)
+        return False
+
+
+def _caps_from_gst(caps) -> list[dict]:
+    return _stage.parse_caps(caps.to_string())
+
+
+def _structure_to_dict(caps) -> dict:
+    return _stage.parse_caps(caps.to_string())[0]
+
+
+def element_class():
+    """Build (once) and return the B200PreEncode GObject class. Needs PyGObject + GStreamer >= 1.22."""
+    global _element_class
+    if _element_class is not None:
+        return _element_class
+    import gi
+    gi.require_version("Gst", "1.0")
+    gi.require_version("GstBase", "1.0")
+    from gi.repository import GObject, Gst, GstBase
+
+    class B200PreEncode(GstBase.BaseTransform):
+        __gstmetadata__ = ("B200 pre-encode stage", "Filter/Converter/Video/Scaler",
+                           "BGRx/RGBx to NV12/I420 (+bilinear shrink) with a 16x16 damage map, fused on sm_100a",
+                           "selkies_gstreamer_b200")
+        __gsttemplates__ = (
+            Gst.PadTemplate.new("sink", Gst.PadDirection.SINK, Gst.PadPresence.ALWAYS,
+                                Gst.Caps.from_string(_stage.SINK_TEMPLATE)),
+            Gst.PadTemplate.new("src", Gst.PadDirection.SRC, Gst.PadPresence.ALWAYS,
+                                Gst.Caps.from_string(_stage.SRC_TEMPLATE)),
+        )
+        # `qos` is inherited from GstBaseTransform (the reference sets it: gstwebrtc_app.py:613, :277).
+        __gproperties__ = {
+            "n-threads": (GObject.TYPE_UINT, "n-threads", "accepted for videoconvert compatibility (gstwebrtc_app.py:612)",
+                          0, GObject.G_MAXUINT, 1, GObject.ParamFlags.READWRITE),
+            "cuda-device-id": (GObject.TYPE_INT, "cuda-device-id", "GPU to run on, -1 = default (gstwebrtc_app.py:264-272)",
+                               -1, GObject.G_MAXINT, -1, GObject.ParamFlags.READWRITE),
+            "method": (GObject.TYPE_STRING, "method", "videoscale method; only 'bilinear'", "bilinear",
+                       GObject.ParamFlags.READWRITE),
+            "add-borders": (GObject.TYPE_BOOLEAN, "add-borders", "videoscale add-borders; only False", False,
+                            GObject.ParamFlags.READWRITE),
+            "damage": (GObject.TYPE_BOOLEAN, "damage", "produce the per-16x16 damage map", True,
+                       GObject.ParamFlags.READWRITE),
+            "damaged-blocks": (GObject.TYPE_UINT, "damaged-blocks", "damaged macroblocks in the last frame",
+                               0, GObject.G_MAXUINT, 0, GObject.ParamFlags.READABLE),
+            "frames": (GObject.TYPE_UINT64, "frames", "frames converted since the last caps change",
+                       0, GObject.G_MAXUINT64, 0, GObject.ParamFlags.READABLE),
+        }
+
+        def __init__(self):
+            super().__init__()
+            self.core = _stage.PreEncodeStage(self.get_name() or FACTORY_NAME)
+            self.set_qos_enabled(True)      # videoconvert's default; late frames are dropped before transform
+            self.set_passthrough(False)
+            self.set_in_place(False)
+
+        def do_get_property(self, prop):
+            return self.core.get_property(prop.name)
+
+        def do_set_property(self, prop, value):
+            self.core.set_property(prop.name, value)
+
+        def do_start(self):
+            return self.core.start()
+
+        def do_stop(self):
+            return self.core.stop()
+
+        def do_transform_caps(self, direction, caps, filter_caps):
+            d = _stage.SINK if direction == Gst.PadDirection.SINK else _stage.SRC
+            filt = _caps_from_gst(filter_caps) if filter_caps is not None else None
+            out = self.core.transform_caps(d, _caps_from_gst(caps), filt)
+            return Gst.Caps.from_string(_stage.caps_to_string(out)) if out else Gst.Caps.new_empty()
+
+        def do_fixate_caps(self, direction, caps, othercaps):
+            d = _stage.SINK if direction == Gst.PadDirection.SINK else _stage.SRC
+            st = self.core.fixate_caps(d, _caps_from_gst(caps), _caps_from_gst(othercaps))
+            return Gst.Caps.from_string(_stage.caps_to_string([st])).fixate()
+
+        def do_set_caps(self, incaps, outcaps):
+            ok = self.core.set_caps(_structure_to_dict(incaps), _structure_to_dict(outcaps))
+            if not ok:
+                Gst.error(f"{FACTORY_NAME}: {self.core.last_error}")
+            return ok
+
+        def do_get_unit_size(self, caps):
+            try:
+                return True, self.core.get_unit_size(_structure_to_dict(caps))
+            except (KeyError, _stage.StageError):
+                return False, 0
+
+        def do_transform(self, inbuf, outbuf):
+            try:
+                with _mapped(Gst, inbuf, write=False) as src, _mapped(Gst, outbuf, write=True) as dst:
+                    rc = self.core.transform(src.ptr, src.size, dst.ptr, dst.size)
+            except _MapError as e:
+                self.core.last_error = str(e)
+                rc = _stage.FLOW_ERROR
+            if rc == _stage.FLOW_OK:
+                return Gst.FlowReturn.OK
+            # Surfaces as a bus ERROR message, which the reference's bus_call handles (gstwebrtc_app.py:1654-1674).
+            Gst.error(f"{FACTORY_NAME}: {self.core.last_error}")
+            return Gst.FlowReturn.NOT_NEGOTIATED if rc == _stage.FLOW_NOT_NEGOTIATED else Gst.FlowReturn.ERROR
+
+    _element_class = B200PreEncode
+    return _element_class
+
+
+def register(rank: int | None = None) -> bool:
+    """Register the factory in-process (no plugin file needed; check_plugins() at
+    gstwebrtc_app.py:1123-1172 therefore needs no new entry)."""
+    import gi
+    gi.require_version("Gst", "1.0")
+    from gi.repository import GObject, Gst
+    cls = element_class()
+    gtype = GObject.type_register(cls) if hasattr(GObject, "type_register") else cls.__gtype__
+    return Gst.Element.register(None, FACTORY_NAME, Gst.Rank.NONE if rank is None else rank, gtype)

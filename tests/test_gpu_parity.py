@@ -332,3 +332,42 @@ def test_linearity_property_on_luma_at_4k():
         d = yb - ya
         assert d.min() >= (157 * 32) // 256 and d.max() <= (157 * 32) // 256 + 1
         assert rb.damaged_count == 240 * 135
+
+
+# ---- the element logic on the GPU ---------------------------------------------------
+def test_stage_transform_and_renegotiation():
+    from selkies_gstreamer_b200 import stage as st
+    seen = []
+    s = st.PreEncodeStage()
+    s.set_property("n-threads", 4)
+    s.set_property("qos", True)
+    s.on_damage = lambda stage, m, n: seen.append(n)
+    sink = st.parse_caps("video/x-raw, format=(string)BGRx, width=(int)1280, height=(int)720, framerate=(fraction)60/1")
+    other = s.transform_caps(st.SINK, sink, st.parse_caps("video/x-raw, format=(string)I420"))
+    fixed = s.fixate_caps(st.SINK, sink, other)
+    assert s.start() and s.set_caps(sink[0], fixed), s.last_error
+    f0 = synth.desktop(1280, 720)
+    f1 = synth.mutate(f0, 0.02, seed=4, aligned=False)
+    out0, m0, n0 = s.transform_array(f0)
+    out1, m1, n1 = s.transform_array(f1)
+    e0 = o.convert(f0, out_fmt=o.OUT_I420, matrix=1, chroma_site=1)      # 720p default: bt709 + h-cosited
+    e1 = o.convert(f1, out_fmt=o.OUT_I420, matrix=1, chroma_site=1)
+    assert (out0 == e0).all() and (out1 == e1).all()
+    em, en = o.damage(1280, 720, o.OUT_I420, e1, e0)
+    assert m0.all() and (m1 == em).all() and n1 == en and seen == [n0, n1]
+    assert s.get_property("damaged-blocks") == en and s.get_property("frames") == 2
+    assert s.src_caps_fields() == {"colorimetry": "bt709", "chroma-site": "mpeg2"}
+    # framerate-only renegotiation keeps the session and the history (set_framerate, gstwebrtc_app.py:1264-1266)
+    sink2 = dict(sink[0], framerate=30)
+    assert s.set_caps(sink2, fixed)
+    _, _, n2 = s.transform_array(f1)
+    assert n2 == 0
+    # a resize recreates it: next frame has no predecessor
+    small_in = dict(sink[0], width=640, height=360)
+    small_out = dict(fixed, width=640, height=360)
+    assert s.set_caps(small_in, small_out)
+    _, m3, n3 = s.transform_array(synth.desktop(640, 360))
+    assert m3.all() and n3 == 40 * 23
+    # buffers that are too small are flow errors, not crashes
+    assert s.transform(f0.ctypes.data, 16, out0.ctypes.data, out0.nbytes) == st.FLOW_ERROR
+    assert s.stop()
