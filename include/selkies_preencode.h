@@ -167,6 +167,48 @@ int sk_last_kernel_us(sk_session *s, float *us);
 int sk_marker_record(sk_session *s, int which);
 int sk_marker_elapsed_us(sk_session *s, float *us);
 
+/*
+ * Convert (and shrink) ONE frame on buffers the caller owns, without allocating anything.
+ * This entry point has no counterpart in the reference.
+ *
+ * It exists for callers that must not allocate GPU memory when they need a frame converted:
+ * a host that is already streaming many desktop sessions on the GPU (cudaMalloc/cudaFree
+ * stall the whole device, so every running session would drop a frame), or a host whose
+ * GPU memory belongs to somebody else's pool (an encoder's buffer pool, a framework's
+ * caching allocator) and is fully handed out.  No cudaMalloc, cudaFree or other allocating
+ * call is made here, on any path.
+ *
+ * The kernel is the shrink+convert+damage kernel of the session path (equal sizes are
+ * allowed).  Its scratch — the two reduction words of the damage count and one vertical
+ * tap entry per output row — lives in a fixed array inside the library image, about 26 KB
+ * on every GPU that loads the library, for the life of the process.  Hence the limit:
+ * out_height <= SK_NOALLOC_MAX_OUT_HEIGHT, anything taller is refused with SK_ERR_ARG
+ * and a message in errbuf (use a session for it).
+ *
+ *   cfg        geometry, formats, matrix, chroma_site, scale_variant, SK_FLAG_NO_DAMAGE as
+ *              for sk_session_create; device_id < 0 means the calling thread's current
+ *              device, otherwise that device is made current.  n_inflight is ignored.
+ *   d_in       device pointer to the BGRx/RGBx frame, rows in_stride bytes apart (0 = 4*width)
+ *   d_out      device pointer to frame_bytes of output (GstVideoInfo default layout)
+ *   d_prev     device pointer to the previous output frame, or NULL (map = all ones)
+ *   d_map      device pointer to ceil(out_h/16)*ceil(out_w/16) bytes
+ *   d_count    device pointer to one uint32 (the damaged-block count)
+ *   cuda_stream  a cudaStream_t; the work is queued there and the call returns at once
+ *   errbuf     optional buffer for a human-readable error, errbuf_len bytes
+ * All device pointers and in_stride must be 4-byte aligned.
+ *
+ * The first call on each GPU looks up where that GPU keeps the array
+ * (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ * All calls share the one array, which still holds what the previous call left there;
+ * each call re-zeroes the reduction words and rewrites the tap entries on cuda_stream
+ * before its kernel.  Two calls whose GPU work can overlap (different streams, or
+ * different host threads) therefore race on the array: serialise them.
+ */
+#define SK_NOALLOC_MAX_OUT_HEIGHT 4320
+int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, size_t in_stride,
+                           void *d_out, const void *d_prev, uint8_t *d_map, uint32_t *d_count,
+                           void *cuda_stream, char *errbuf, size_t errbuf_len);
+
 /* Number of kernel launches issued by this library in this process so far. */
 uint64_t sk_launch_count(void);
 

@@ -24,13 +24,14 @@ SK_SCALE_VARIANT_GST_LQ, SK_SCALE_VARIANT_PLAIN_LQ = 0, 1
 SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING = 1, 2, 4
 SK_MAX_BATCH = 32
 SK_ABI_VERSION = 1
+SK_NOALLOC_MAX_OUT_HEIGHT = 4320
 
 # Every symbol include/selkies_preencode.h declares (tests check the .so exports all of them).
 EXPORTS = (
     "sk_session_create", "sk_session_destroy", "sk_get_input_staging", "sk_get_device_input",
     "sk_upload", "sk_submit", "sk_submit_device", "sk_wait", "sk_reset_history",
     "sk_batch_submit", "sk_batch_wait", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
-    "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
+    "sk_scale_frame_noalloc", "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
 )
 
 
@@ -74,7 +75,7 @@ class PreencodeLibraryError(RuntimeError):
 
 def build(force: bool = False) -> str:
     """Compile the library in-tree with nvcc for sm_100a (seconds; works without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in ("sk_kernels.cu", "sk_session.cu", "sk_kernels.h")]
+    srcs = [os.path.join(CSRC, f) for f in ("sk_kernels.cu", "sk_session.cu", "sk_noalloc.cu", "sk_kernels.h")]
     srcs.append(os.path.join(_PKG, "..", "include", "selkies_preencode.h"))
     stale = (not os.path.exists(LIB_PATH)
              or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(s) for s in srcs))
@@ -114,6 +115,7 @@ def load() -> ctypes.CDLL:
         "sk_last_kernel_us": (i, [vp, fp]),
         "sk_marker_record": (i, [vp, i]),
         "sk_marker_elapsed_us": (i, [vp, fp]),
+        "sk_scale_frame_noalloc": (i, [ctypes.POINTER(SkConfig), vp, sz, vp, vp, vp, vp, vp, ctypes.c_char_p, sz]),
         "sk_launch_count": (u64, []),
         "sk_last_error": (ctypes.c_char_p, [vp]),
         "sk_version": (i, []),
