@@ -498,6 +498,267 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
     }
 }
 
+// ---- tiled scale kernel (fast path) -------------------------------------------------
+// Used when the horizontal pass comes first (or only one axis changes) and the source
+// rows of a 16-row output tile fit the shared-memory window.  Two passes per CTA tile of
+// 128 x 16 output pixels:
+//   A  every needed source row is h-scaled ONCE into shared memory; lanes own adjacent
+//      output columns, so a warp's gathers touch ~2 cache lines instead of ~6;
+//   B  each thread takes 4 adjacent output pixels x 2 rows with 128-bit LDS, applies the
+//      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
+constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
+
+__device__ __forceinline__ uint32_t lerp_h2(uint32_t a, uint32_t b, uint32_t f)
+{
+    const uint32_t w1 = f, w0 = 256u - f;
+    uint32_t e = (a & 0x00ff00ffu) * w0 + (b & 0x00ff00ffu) * w1;
+    uint32_t o = __byte_perm(a, 0, 0x4341) * w0 + __byte_perm(b, 0, 0x4341) * w1;
+    return __byte_perm(e, o, 0x7351);           // byte 1 of every 16-bit lane = (..)>>8
+}
+__device__ __forceinline__ uint32_t lerp_v2(uint32_t a, uint32_t b, uint32_t p)
+{
+    const uint32_t w1 = p, w0 = 64u - p;
+    uint32_t e = (a & 0x00ff00ffu) * w0 + ((b & 0x00ff00ffu) * w1 + 0x00200020u);
+    uint32_t o = __byte_perm(a, 0, 0x4341) * w0 + (__byte_perm(b, 0, 0x4341) * w1 + 0x00200020u);
+    return ((e >> 6) & 0x00ff00ffu) | ((o << 2) & 0xff00ff00u);
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async8(uint32_t smem_addr, const void *g)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_addr), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit_wait()
+{
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, bool FULL>
+__device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
+                                           const int bx0, const int by0, const int lane, const int warp,
+                                           const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out)
+{
+    const int w = g.out_w, h = g.out_h;
+
+    // source-row window of this tile
+    const int ylast = FULL ? by0 + 15 : min(by0 + 15, h - 1);
+    int sy0 = by0, sy1 = ylast;
+    if (SV) {
+        sy0 = f.v_off[by0];
+        sy1 = min(f.v_off[ylast] + 1, g.in_h - 1);
+    }
+    const int nr = sy1 - sy0 + 1;
+
+    // Previous-frame words of pass B do not depend on shared memory: fetch them first so their
+    // latency hides behind pass A.
+    const int y0 = by0 + 2 * warp;
+    const int x = bx0 + lane * 4;
+    const int nvx = FULL ? 4 : ((w - x) >= 4 ? 4 : ((w - x) > 0 ? 2 : 0));
+    const bool rows_valid = FULL || y0 < h;
+    const int nv = rows_valid ? nvx : 0;
+    nvx_out = nvx;
+    rows_valid_out = rows_valid;
+    const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
+    const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
+    uint32_t pyw[2] = {0, 0}, pcw = 0;
+    if (DAMAGE && have_prev) {
+        if (FULL) {
+            pyw[0] = ld4<0>(f.prev + y_off);
+            pyw[1] = ld4<0>(f.prev + y_off + g.y_stride);
+            if (FMT == 0) pcw = ld4<0>(f.prev + g.off_c0 + c_off);
+            else pcw = ld2<0>(f.prev + g.off_c0 + c_off) | (ld2<0>(f.prev + g.off_c1 + c_off) << 16);
+        } else {
+            pyw[0] = load_word<0>(f.prev + y_off, nv);
+            pyw[1] = load_word<0>(f.prev + y_off + g.y_stride, nv);
+            if (FMT == 0) {
+                pcw = load_word<0>(f.prev + g.off_c0 + c_off, nv);
+            } else {
+                uint32_t a = 0, b = 0;
+                if (nv == 4) { a = ld2<0>(f.prev + g.off_c0 + c_off); b = ld2<0>(f.prev + g.off_c1 + c_off); }
+                else if (nv == 2) { a = ld1(f.prev + g.off_c0 + c_off); b = ld1(f.prev + g.off_c1 + c_off); }
+                pcw = a | (b << 16);
+            }
+        }
+    }
+
+    // ---- stage: the raw source window of this tile, global -> shared with cp.async (no registers,
+    //      so many CTAs per SM keep their copies in flight while others compute)
+    const int xo_first = bx0 > 0 ? bx0 - 1 : 0;                       // halo column included
+    const int xo_last = FULL ? bx0 + 127 : min(bx0 + 127, w - 1);
+    int xs_first = xo_first, xs_last = xo_last;
+    if (SH) {
+        xs_first = (xo_first * g.h_inc) >> 16;
+        xs_last = ((xo_last * g.h_inc) >> 16) + 1;
+    }
+    const int cx0 = xs_first & ~3;                                    // 16-byte aligned start
+    const int nch = ((xs_last - cx0) >> 2) + 1;
+    const uint32_t RS = (uint32_t)g.scale_raw_stride;                 // words per raw row
+    {
+        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0;
+        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW);
+        for (int r = warp; r < nr; r += 8) {
+            const uint8_t *row = base + (size_t)r * (size_t)g.in_stride;
+            for (int c = lane; c < nch; c += 32) {
+                const uint32_t dst = raw_s + 4u * ((uint32_t)r * RS + 4u * (uint32_t)c);
+                if (cx0 + 4 * c + 4 <= g.in_w) cp_async16(dst, row + 16 * c);
+                else cp_async8(dst, row + 16 * c);     // in_w is even: a row may end in a 2-pixel chunk
+            }
+        }
+        cp_async_commit_wait();
+    }
+    __syncthreads();
+
+    // ---- pass A: h-scale (or copy) the window once into the second shared buffer; lanes own
+    //      adjacent output columns, so the gathers are (nearly) bank-conflict free
+    {
+        uint32_t rel[4], fr[4];
+        bool cv[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int xo = bx0 + lane + 32 * k;
+            cv[k] = FULL || xo < w;
+            const int xc = cv[k] ? xo : xo_last;
+            rel[k] = (uint32_t)(xc - cx0);
+            fr[k] = 0;
+            if (SH) {
+                const int32_t acc = xc * g.h_inc;
+                rel[k] = (uint32_t)((acc >> 16) - cx0);
+                fr[k] = (uint32_t)(acc >> 8) & 0xffu;
+            }
+        }
+        const bool want_halo = SITE == 1 && lane == 0 && bx0 > 0;
+        uint32_t hrel = (uint32_t)(xo_first - cx0), hf = 0;
+        if (SH) {
+            const int32_t acc = xo_first * g.h_inc;
+            hrel = (uint32_t)((acc >> 16) - cx0);
+            hf = (uint32_t)(acc >> 8) & 0xffu;
+        }
+        for (int r = warp; r < nr; r += 8) {
+            const uint32_t *R = RAW + (uint32_t)r * RS;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t a = R[rel[k]];
+                S[r][lane + 32 * k] = SH ? lerp_h2(a, R[rel[k] + 1], fr[k]) : a;
+            }
+            if (want_halo) S[r][128] = SH ? lerp_h2(R[hrel], R[hrel + 1], hf) : R[hrel];
+        }
+    }
+    __syncthreads();
+
+    // ---- pass B: vertical 2-tap + matrix + chroma + stores + compare
+    uint32_t hh[2][2];
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++) {
+        const int y = y0 + rr;
+        uint4 q = make_uint4(0, 0, 0, 0);
+        uint32_t hp = 0;
+        if (rows_valid) {
+            int ra = y - sy0, rb = ra;
+            uint32_t p = 0;
+            if (SV) {
+                const int o = f.v_off[y];
+                p = (uint32_t)f.v_tap[y];
+                ra = o - sy0;
+                rb = min(o + 1, g.in_h - 1) - sy0;
+            }
+            q = *reinterpret_cast<const uint4 *>(&S[ra][4 * lane]);
+            if (SV) {
+                const uint4 q2 = *reinterpret_cast<const uint4 *>(&S[rb][4 * lane]);
+                q.x = lerp_v2(q.x, q2.x, p);
+                q.y = lerp_v2(q.y, q2.y, p);
+                q.z = lerp_v2(q.z, q2.z, p);
+                q.w = lerp_v2(q.w, q2.w, p);
+            }
+            if (SITE == 1 && lane == 0) {          // only the warp's first lane needs the halo pixel
+                hp = S[ra][128];
+                if (SV) hp = lerp_v2(hp, S[rb][128], p);
+            }
+        }
+        uint32_t yw, uv[4];
+        matrix_quad(q, g, yw, uv);
+        uint32_t left = 0;
+        if (SITE == 1) {
+            left = __shfl_up_sync(kFull, uv[3], 1);
+            if (lane == 0) {
+                uint32_t au = dp4a_us(hp, g.cu, 32768);
+                uint32_t av = dp4a_us(hp, g.cv, 32768);
+                left = __byte_perm(au, av, 0x7531);
+            }
+        }
+        chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
+        uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
+        if (FULL) *reinterpret_cast<uint32_t *>(oy) = yw;
+        else store_word(oy, yw, nv);
+        if (DAMAGE) diff |= (yw ^ pyw[rr]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
+    }
+    {
+        uint32_t cw = chroma_v<FMT>(hh[0][0], hh[0][1], hh[1][0], hh[1][1]);
+        if (FMT == 0) {
+            if (FULL) *reinterpret_cast<uint32_t *>(f.out + g.off_c0 + c_off) = cw;
+            else store_word(f.out + g.off_c0 + c_off, cw, nv);
+            if (DAMAGE) diff |= (cw ^ pcw) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
+        } else {
+            uint8_t *pu = f.out + g.off_c0 + c_off;
+            uint8_t *pv = f.out + g.off_c1 + c_off;
+            if (nv == 4) {
+                *reinterpret_cast<unsigned short *>(pu) = (unsigned short)cw;
+                *reinterpret_cast<unsigned short *>(pv) = (unsigned short)(cw >> 16);
+            } else if (nv == 2) {
+                *pu = (uint8_t)cw;
+                *pv = (uint8_t)(cw >> 16);
+            }
+            if (DAMAGE) diff |= (cw ^ pcw) & ((FULL || nvx == 4) ? 0xffffffffu : 0x00ff00ffu);
+        }
+    }
+}
+
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV>
+__global__ void __launch_bounds__(kThreads, 6)
+sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+{
+    extern __shared__ __align__(16) uint32_t sk_smem[];
+    uint32_t (*S)[kScaleRowWords] = reinterpret_cast<uint32_t (*)[kScaleRowWords]>(sk_smem);
+    uint32_t *RAW = sk_smem + (size_t)g.scale_rows * kScaleRowWords;
+    const SkFrame &f = batch.f[blockIdx.z];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int bx0 = blockIdx.x * 128;
+    const int by0 = blockIdx.y * 16;
+    const bool have_prev = DAMAGE && (f.prev != nullptr);
+    const bool full = (bx0 + 128 <= g.out_w) && (by0 + 16 <= g.out_h);
+
+    uint32_t diff = 0;
+    int nvx = 0;
+    bool rows_valid = false;
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
+
+    if (DAMAGE) {
+        __shared__ uint32_t s_mask[8];
+        bool d = rows_valid && nvx > 0 && (diff != 0 || !have_prev);
+        uint32_t m = __ballot_sync(kFull, d);
+        if (lane == 0) s_mask[warp] = m;
+        __syncthreads();
+        bool hit = false;
+        if (threadIdx.x < 8) {
+            uint32_t acc = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) acc |= s_mask[k];
+            const bool flag = ((acc >> (4 * threadIdx.x)) & 0xfu) != 0;
+            const int bx = blockIdx.x * 8 + threadIdx.x, by = blockIdx.y;
+            if (bx < g.mb_w && by < g.mb_h) {
+                f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                hit = flag;
+            }
+        }
+        const int total = __syncthreads_count(hit);
+        if (threadIdx.x == 0) finish_count(f, (uint32_t)total);
+    }
+}
+
 template <int RP, int QX, int HINT>
 cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
 {
@@ -543,6 +804,24 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream
 {
     dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
     dim3 block(kThreads);
+    if (g.scale_fast) {
+        const size_t smem = (size_t)g.scale_rows * (kScaleRowWords + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
+#define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
+        (g.scale_v != 0) == SV) {                                                                     \
+        auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV>;                                    \
+        if (smem > 48 * 1024)                                                                         \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
+        kern<<<grid, block, smem, st>>>(g, b);                                                        \
+        return cudaGetLastError();                                                                    \
+    }
+#define SK_TILED_MODES(FMT, SITE, DMG) \
+    SK_TILED(FMT, SITE, DMG, true, true) SK_TILED(FMT, SITE, DMG, true, false) SK_TILED(FMT, SITE, DMG, false, true)
+        SK_TILED_MODES(0, 0, true) SK_TILED_MODES(0, 1, true) SK_TILED_MODES(1, 0, true) SK_TILED_MODES(1, 1, true)
+        SK_TILED_MODES(0, 0, false) SK_TILED_MODES(0, 1, false) SK_TILED_MODES(1, 0, false) SK_TILED_MODES(1, 1, false)
+#undef SK_TILED_MODES
+#undef SK_TILED
+    }
 #define SK_CASE(FMT, SITE, DMG)                                                  \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {           \
         sk_scale_kernel<FMT, SITE, DMG><<<grid, block, 0, st>>>(g, b);           \

@@ -22,6 +22,9 @@ struct SkGeom {
     int32_t h_inc;            // 16.16 edge-aligned increment
     int h_first;              // order of the two 2-tap passes
     int scale_h, scale_v;     // which axes actually change size
+    int scale_fast;           // 1: the shared-memory tiled kernel applies (set by the session runtime)
+    int scale_rows;           // tiled kernel: most source rows any 16-row output tile needs
+    int scale_raw_stride;     // tiled kernel: words per staged raw row (widest tile window, 16-byte chunks)
 };
 
 // Per-session pointers of one launch (all device memory).

@@ -27,6 +27,7 @@ namespace {
 constexpr int kMaxInflight = 8;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_variant{0};
+std::atomic<int> g_scale_generic{0};   // tuning/testing: force the generic scale kernel
 thread_local std::string g_create_error;
 
 inline int ru(int v, int a) { return (v + a - 1) / a * a; }
@@ -304,6 +305,10 @@ uint64_t sk_launch_count(void) { return g_launches.load(); }
 
 int sk_set_kernel_variant(int variant)
 {
+    if (variant == 100 || variant == 101) {     // 100: force the generic scale kernel for new sessions; 101: default
+        g_scale_generic.store(variant == 100 ? 1 : 0);
+        return SK_OK;
+    }
     if (variant < 0 || variant > 15) return SK_ERR_ARG;
     g_variant.store(variant);
     return SK_OK;
@@ -434,6 +439,37 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         std::vector<int32_t> off;
         std::vector<int16_t> tap;
         vertical_taps(g.in_h, g.out_h, c.scale_variant, off, tap);
+        // The tiled kernel needs the h pass first (or a single axis) and every 16-row output
+        // tile's source rows inside its shared-memory window (36 rows).
+        int max_rows = 16;
+        if (g.scale_v) {
+            max_rows = 0;
+            for (int by0 = 0; by0 < g.out_h; by0 += 16) {
+                const int ylast = (by0 + 15 < g.out_h) ? by0 + 15 : g.out_h - 1;
+                int last = off[ylast] + 1;
+                if (last > g.in_h - 1) last = g.in_h - 1;
+                const int rows = last - off[by0] + 1;
+                if (rows > max_rows) max_rows = rows;
+            }
+        }
+        // widest raw window (in 16-byte chunks) any 128-column output tile stages
+        int max_chunks = 0;
+        for (int bx0 = 0; bx0 < g.out_w; bx0 += 128) {
+            const int xo_first = bx0 > 0 ? bx0 - 1 : 0;
+            const int xo_last = (bx0 + 127 < g.out_w) ? bx0 + 127 : g.out_w - 1;
+            int xs_first = xo_first, xs_last = xo_last;
+            if (g.scale_h) {
+                xs_first = (int)(((int64_t)xo_first * g.h_inc) >> 16);
+                xs_last = (int)(((int64_t)xo_last * g.h_inc) >> 16) + 1;
+            }
+            const int chunks = ((xs_last - (xs_first & ~3)) >> 2) + 1;
+            if (chunks > max_chunks) max_chunks = chunks;
+        }
+        g.scale_rows = max_rows;
+        g.scale_raw_stride = 4 * max_chunks;
+        const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
+        const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
+        g.scale_fast = (order_ok && smem <= 96 * 1024 && g_scale_generic.load() == 0) ? 1 : 0;
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));

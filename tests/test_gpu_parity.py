@@ -214,12 +214,28 @@ def test_convert_only_mode():
 @pytest.mark.parametrize("dims", [(2560, 1440, 1920, 1080), (64, 48, 32, 24), (100, 60, 98, 34), (64, 48, 64, 24),
                                   (64, 48, 30, 48), (64, 64, 16, 60), (1920, 1080, 1280, 720), (3840, 2160, 1920, 1080)])
 @pytest.mark.parametrize("variant", [0, 1])
-def test_scale_parity(dims, variant):
+@pytest.mark.parametrize("kernel", ["tiled", "generic"])
+def test_scale_parity(dims, variant, kernel):
+    """Both scale kernels (shared-memory tiled fast path, generic gather) against the oracle."""
     w, h, ow, oh = dims
     f0 = rand_frame(w, h, w + oh + variant)
     f1 = synth.mutate(f0, 0.03, seed=variant, aligned=False)
-    for out_format, site in (("I420", 1), ("NV12", 0)):
-        check_sequence([f0, f1], w, h, out_w=ow, out_h=oh, variant=variant, out_format=out_format, chroma_site=site)
+    lib = _abi.load()
+    try:
+        lib.sk_set_kernel_variant(100 if kernel == "generic" else 101)
+        for out_format, site in (("I420", 1), ("NV12", 0)):
+            check_sequence([f0, f1], w, h, out_w=ow, out_h=oh, variant=variant, out_format=out_format, chroma_site=site)
+    finally:
+        lib.sk_set_kernel_variant(101)
+
+
+@pytest.mark.parametrize("dims", [(1366, 768, 1280, 720), (258, 130, 130, 66), (2560, 1440, 1278, 720), (514, 96, 258, 90)])
+def test_scale_ragged_edges(dims):
+    w, h, ow, oh = dims
+    f0 = rand_frame(w, h, w * 3 + oh)
+    f1 = synth.mutate(f0, 0.05, seed=2, aligned=False)
+    for out_format, site in (("NV12", 1), ("I420", 0)):
+        check_sequence([f0, f1, f1], w, h, out_w=ow, out_h=oh, out_format=out_format, chroma_site=site)
 
 
 def test_config3_desktop_content_bt709():
