@@ -274,7 +274,8 @@ def run_b200(args, rank, world, local_rank, dist):
         s.close()
     Se = min(args.e2e_sessions, S)
     esess = [sk.PreencodeSession(W, H, out_format="NV12", colorimetry="bt709", chroma_site="mpeg2",
-                                 device_id=local_rank, n_inflight=2, host_output=True) for _ in range(Se)]
+                                 device_id=local_rank, n_inflight=2, host_output=True, timing=(i == 0))
+             for i in range(Se)]
     for s, (a, b) in zip(esess, inputs):
         s.upload(0, a)
         s.upload(1, b)
@@ -302,6 +303,15 @@ def run_b200(args, rank, world, local_rank, dist):
         e2e_t = float(t[0])
     e2e_fps = Se * esteps * world / e2e_t
     frame_bytes = esess[0].frame_bytes
+    # PCIe in isolation (north_star: the copies are reported separately from the HBM roofline):
+    # one session, one frame at a time, CUDA events around its H2D and D2H.
+    h2d, d2h = [], []
+    for k in range(8):
+        rr = esess[0].wait(esess[0].submit(k & 1))
+        h2d.append(rr.h2d_us); d2h.append(rr.d2h_us)
+    pcie = {"h2d_gbs_isolated": 4 * W * H / (statistics.median(h2d) * 1e-6) / 1e9,
+            "d2h_gbs_isolated": (frame_bytes + ((W // 16) * (H // 16) + 4)) / (statistics.median(d2h) * 1e-6) / 1e9,
+            "how": "median of 8 single-frame submits, CUDA events around cudaMemcpyAsync from/to pinned memory"}
     meta_bytes = ((r.damage_map.size + 3) // 4) * 4 + 4
     for s in esess:
         s.close()
@@ -333,6 +343,7 @@ def run_b200(args, rank, world, local_rank, dist):
                 "h2d_gbs_per_gpu": e2e_fps / world * 4 * W * H / 1e9,
                 "d2h_gbs_per_gpu": e2e_fps / world * (frame_bytes + meta_bytes) / 1e9,
                 "timing": "wall clock between host syncs, max over ranks"},
+        "pcie": pcie,
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
