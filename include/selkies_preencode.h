@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SK_ABI_VERSION 1
+#define SK_ABI_VERSION 2
 
 /* status codes */
 enum {
@@ -64,7 +64,9 @@ enum { SK_SCALE_VARIANT_GST_LQ = 0, SK_SCALE_VARIANT_PLAIN_LQ = 1 };
 enum {
     SK_FLAG_NO_DAMAGE   = 1 << 0,  /* convert-only: no previous-frame read, no map                   */
     SK_FLAG_HOST_OUTPUT = 1 << 1,  /* copy the converted frame back to pinned host memory each frame */
-    SK_FLAG_TIMING      = 1 << 2   /* record CUDA events; sk_result.*_us are filled                  */
+    SK_FLAG_TIMING      = 1 << 2,  /* record CUDA events; sk_result.*_us are filled                  */
+    SK_FLAG_POLICY      = 1 << 3   /* keep per-macroblock temporal counters in the kernel and return
+                                      the SK_POLICY_* map (hot / paint-over), see below              */
 };
 
 typedef struct sk_session sk_session;
@@ -87,7 +89,19 @@ typedef struct sk_config {
     int32_t  scale_variant;   /* SK_SCALE_VARIANT_*                                                */
     int32_t  n_inflight;      /* staging slots and output ring depth, 2..8 (0 = 2)                 */
     uint32_t flags;           /* SK_FLAG_*                                                         */
+    /* Temporal damage policy, the knobs the reference hands to its capture module
+     * (src/selkies/selkies.py:2949-2951); 0 = that default; each 1..255.                         */
+    int32_t  damage_block_threshold;     /* consecutive damaged frames that make a block "hot" (10) */
+    int32_t  damage_block_duration;      /* frames a hot block stays hot after its last change (20) */
+    int32_t  paint_over_trigger_frames;  /* still frames after which a changed block is repainted (15) */
 } sk_config;
+
+/* Per-macroblock policy flags (sk_result.host_policy_map), updated inside the convert kernel. */
+enum {
+    SK_POLICY_DAMAGED    = 1,  /* differs from the previous frame (same as the damage map)          */
+    SK_POLICY_HOT        = 2,  /* has kept changing: treat as motion, hold quality, no paint-over   */
+    SK_POLICY_PAINT_OVER = 4   /* went still long enough: send one high-quality refresh now         */
+};
 
 /* What one converted frame looks like to the caller (GstVideoInfo default layout). */
 typedef struct sk_result {
@@ -102,6 +116,8 @@ typedef struct sk_result {
     int32_t  mb_w, mb_h;
     uint32_t damaged_count;       /* exact sum of the map                                         */
     float    h2d_us, kernel_us, d2h_us;   /* only with SK_FLAG_TIMING                             */
+    const uint8_t *host_policy_map; /* pinned, uint8[mb_h][mb_w] of SK_POLICY_* bits; NULL without SK_FLAG_POLICY */
+    const uint8_t *dev_policy_map;
 } sk_result;
 
 /* Replaces: Gst.ElementFactory.make("videoconvert"/"cudaconvert") + set_caps

@@ -69,6 +69,8 @@ def lib() -> ctypes.CDLL:
             fn.argtypes = [u8p, ctypes.c_int]
         L.sko_chroma_down_v2.restype = None
         L.sko_chroma_down_v2.argtypes = [u8p, u8p, ctypes.c_int]
+        L.sko_policy_update.restype = None
+        L.sko_policy_update.argtypes = [ctypes.c_int, u8p, ctypes.POINTER(ctypes.c_uint32), u8p] + [ctypes.c_int] * 3
         _lib = L
     return _lib
 
@@ -131,6 +133,22 @@ def damage(w: int, h: int, fmt: int, cur: np.ndarray, prev: np.ndarray | None):
     m = np.zeros((mbh, mbw), dtype=np.uint8)
     n = lib().sko_damage(w, h, fmt, _u8p(cur), _u8p(prev) if prev is not None else None, _u8p(m))
     return m, int(n)
+
+
+class PolicyTracker:
+    """Host-side replay of the per-macroblock temporal policy (state lives here)."""
+
+    def __init__(self, mb_w: int, mb_h: int, threshold: int = 10, duration: int = 20, trigger: int = 15):
+        self.shape = (mb_h, mb_w)
+        self.state = np.zeros(mb_w * mb_h, dtype=np.uint32)
+        self.knobs = (threshold, duration, trigger)
+
+    def update(self, damage_map: np.ndarray) -> np.ndarray:
+        m = np.ascontiguousarray(damage_map, dtype=np.uint8).reshape(-1)
+        pol = np.zeros(m.size, dtype=np.uint8)
+        lib().sko_policy_update(m.size, _u8p(m), self.state.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
+                                _u8p(pol), *self.knobs)
+        return pol.reshape(self.shape)
 
 
 def split_planes(buf: np.ndarray, w: int, h: int, fmt: int):

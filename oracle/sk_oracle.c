@@ -525,3 +525,37 @@ int sko_damage(int w, int h, int fmt, const uint8_t *cur, const uint8_t *prev, u
     }
     return count;
 }
+
+/* ------------------------------------------------------------------ policy */
+
+void sko_policy_update(int n, const uint8_t *map, uint32_t *state, uint8_t *policy,
+                       int threshold, int duration, int trigger)
+{
+    int i;
+    for (i = 0; i < n; i++) {
+        uint32_t st = state[i];
+        uint32_t streak = st & 0xff, hot = (st >> 8) & 0xff, still = (st >> 16) & 0xff, dirty = (st >> 24) & 1;
+        uint32_t pol = 0;
+        if (map[i]) {
+            streak = streak < 255 ? streak + 1 : 255;
+            still = 0;
+            dirty = 1;
+            if (streak >= (uint32_t)threshold || hot > 0)
+                hot = (uint32_t)duration;
+            pol = 1;
+        } else {
+            streak = 0;
+            still = still < 255 ? still + 1 : 255;
+            if (hot > 0)
+                hot--;
+            if (dirty && hot == 0 && still >= (uint32_t)trigger) {
+                pol = 4;
+                dirty = 0;
+            }
+        }
+        if (hot > 0)
+            pol |= 2;
+        state[i] = streak | (hot << 8) | (still << 16) | (dirty << 24);
+        policy[i] = (uint8_t)pol;
+    }
+}

@@ -71,6 +71,13 @@ int sko_convert(const sko_config *cfg, const uint8_t *in, uint8_t *out);
 int sko_damage(int out_w, int out_h, int out_fmt,
                const uint8_t *cur, const uint8_t *prev, uint8_t *map);
 
+/* Temporal damage policy (definition owned by this project, shaped by the knobs at
+ * src/selkies/selkies.py:2949-2951).  state: one uint32 per macroblock, in/out
+ * (streak | hot<<8 | still<<16 | dirty<<24); policy: one byte per macroblock, out
+ * (1 damaged, 2 hot, 4 paint-over). */
+void sko_policy_update(int n_blocks, const uint8_t *map, uint32_t *state, uint8_t *policy,
+                       int threshold, int duration, int trigger);
+
 /* Chroma filters exposed for known-answer tests: operate on AYUV lines in place. */
 void sko_chroma_down_h2(uint8_t *ayuv, int w);
 void sko_chroma_down_h2_cs(uint8_t *ayuv, int w);

@@ -21,9 +21,10 @@ SK_MATRIX_BT601, SK_MATRIX_BT709, SK_MATRIX_BT2020 = 0, 1, 2
 SK_SITE_NONE, SK_SITE_H_COSITED = 0, 1
 SK_SCALE_BILINEAR = 1
 SK_SCALE_VARIANT_GST_LQ, SK_SCALE_VARIANT_PLAIN_LQ = 0, 1
-SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING = 1, 2, 4
+SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING, SK_FLAG_POLICY = 1, 2, 4, 8
 SK_MAX_BATCH = 32
-SK_ABI_VERSION = 1
+SK_ABI_VERSION = 2
+SK_POLICY_DAMAGED, SK_POLICY_HOT, SK_POLICY_PAINT_OVER = 1, 2, 4
 SK_NOALLOC_MAX_OUT_HEIGHT = 4320
 
 # Every symbol include/selkies_preencode.h declares (tests check the .so exports all of them).
@@ -50,6 +51,9 @@ class SkConfig(ctypes.Structure):
         ("scale_variant", ctypes.c_int32),
         ("n_inflight", ctypes.c_int32),
         ("flags", ctypes.c_uint32),
+        ("damage_block_threshold", ctypes.c_int32),
+        ("damage_block_duration", ctypes.c_int32),
+        ("paint_over_trigger_frames", ctypes.c_int32),
     ]
 
 
@@ -66,6 +70,8 @@ class SkResult(ctypes.Structure):
         ("mb_w", ctypes.c_int32), ("mb_h", ctypes.c_int32),
         ("damaged_count", ctypes.c_uint32),
         ("h2d_us", ctypes.c_float), ("kernel_us", ctypes.c_float), ("d2h_us", ctypes.c_float),
+        ("host_policy_map", ctypes.c_void_p),
+        ("dev_policy_map", ctypes.c_void_p),
     ]
 
 

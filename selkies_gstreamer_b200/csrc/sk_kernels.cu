@@ -143,6 +143,41 @@ __device__ __forceinline__ void finish_count(const SkFrame &f, uint32_t n)
     }
 }
 
+// Temporal policy of one macroblock: consecutive-damage streak, "hot" countdown
+// while a block keeps changing, still-frame counter that triggers one paint-over. Flags:
+// 1 = damaged this frame, 2 = hot (persistently damaged), 4 = paint over now.
+__device__ __forceinline__ void policy_update(const SkFrame &f, const SkGeom &g, size_t idx, bool damaged, uint32_t st)
+{
+    if (f.state == nullptr) return;
+    uint32_t streak = st & 0xffu, hot = (st >> 8) & 0xffu, still = (st >> 16) & 0xffu, dirty = (st >> 24) & 1u;
+    uint32_t pol = 0;
+    if (damaged) {
+        streak = min(streak + 1u, 255u);
+        still = 0;
+        dirty = 1;
+        if (streak >= (uint32_t)g.pol_threshold || hot > 0) hot = (uint32_t)g.pol_duration;
+        pol = 1;
+    } else {
+        streak = 0;
+        still = min(still + 1u, 255u);
+        if (hot > 0) hot--;
+        if (dirty && hot == 0 && still >= (uint32_t)g.pol_trigger) {
+            pol = 4;
+            dirty = 0;
+        }
+    }
+    if (hot > 0) pol |= 2;
+    f.state[idx] = streak | (hot << 8) | (still << 16) | (dirty << 24);
+    f.policy[idx] = (uint8_t)pol;
+}
+// The state word of the macroblock a thread will publish, fetched at kernel entry so that its
+// latency is hidden behind the pixel work instead of sitting on the CTA's tail.
+__device__ __forceinline__ uint32_t policy_prefetch(const SkFrame &f, const SkGeom &g, bool mine, int bx, int by)
+{
+    if (!mine || f.state == nullptr || bx >= g.mb_w || by >= g.mb_h) return 0;
+    return f.state[(size_t)by * g.mb_w + bx];
+}
+
 // ---- no-scale kernel ----------------------------------------------------------
 // CTA = 8 warps.  A warp covers 128*QX pixels of 2*RP rows; lane l owns the
 // quads at x = bx0 + q*128 + 4*l.  The CTA covers 16*RP rows = RP macroblock
@@ -292,8 +327,10 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
     }
 }
 
+// Register budget: RP*QX <= 2 must stay at 5 CTAs/SM (<= 48 registers) — the sweep in profiles/ shows the
+// occupancy cliff costs ~12 % of the HBM rate.
 template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, (RP * QX <= 2) ? 5 : 1)
 sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
 {
     constexpr int ROWS = 2 * RP;
@@ -307,6 +344,12 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 * QX <= g.out_w) && (by0 + 16 * RP <= g.out_h);
 
+    uint32_t pol_state = 0;
+    if (DAMAGE) {
+        const int t = threadIdx.x;
+        pol_state = policy_prefetch(f, g, t < NMB, blockIdx.x * (8 * QX) + ((t % (QX * 8)) / 8) * 8 + t % 8,
+                                    blockIdx.y * RP + t / (QX * 8));
+    }
     uint32_t diff[QX];
     int nvq[QX];
     if (full) convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, true>(g, f, bx0, y0, lane, have_prev, diff, nvq);
@@ -339,6 +382,7 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
             const int by = blockIdx.y * RP + mbrow;
             if (bx < g.mb_w && by < g.mb_h) {
                 f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
                 hit = flag;
             }
         }
@@ -490,7 +534,10 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
                 flag = ((acc >> (4 * lane)) & 0xfu) != 0;
                 int bx = blockIdx.x * 8 + lane, by = blockIdx.y;
                 valid = bx < g.mb_w && by < g.mb_h;
-                if (valid) f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                if (valid) {
+                    f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                    policy_update(f, g, (size_t)by * g.mb_w + bx, flag, f.state ? f.state[(size_t)by * g.mb_w + bx] : 0u);
+                }
             }
             uint32_t votes = __ballot_sync(kFull, valid && flag);
             if (lane == 0) finish_count(f, (uint32_t)__popc(votes));
@@ -730,6 +777,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 <= g.out_w) && (by0 + 16 <= g.out_h);
 
+    const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8, blockIdx.x * 8 + threadIdx.x, blockIdx.y) : 0u;
     uint32_t diff = 0;
     int nvx = 0;
     bool rows_valid = false;
@@ -751,6 +799,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
             const int bx = blockIdx.x * 8 + threadIdx.x, by = blockIdx.y;
             if (bx < g.mb_w && by < g.mb_h) {
                 f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
+                policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
                 hit = flag;
             }
         }

@@ -25,6 +25,8 @@ struct SkGeom {
     int scale_fast;           // 1: the shared-memory tiled kernel applies (set by the session runtime)
     int scale_rows;           // tiled kernel: most source rows any 16-row output tile needs
     int scale_raw_stride;     // tiled kernel: words per staged raw row (widest tile window, 16-byte chunks)
+    // temporal damage policy (per-macroblock saturating counters updated in the same kernel)
+    int pol_threshold, pol_duration, pol_trigger;
 };
 
 // Per-session pointers of one launch (all device memory).
@@ -37,6 +39,8 @@ struct SkFrame {
     uint32_t *scratch;        // [0] running count, [1] CTA ticket; both return to 0 at kernel end
     const int32_t *v_off;     // scale: first source row per output row
     const int16_t *v_tap;     // scale: second vertical tap (6-bit) per output row
+    uint32_t *state;          // per-macroblock policy state (streak | hot<<8 | still<<16 | dirty<<24), or nullptr
+    uint8_t *policy;          // per-macroblock policy flags of this frame (SK_POLICY_*), or nullptr
 };
 
 struct SkBatch {

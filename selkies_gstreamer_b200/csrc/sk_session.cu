@@ -42,7 +42,7 @@ struct Slot {          // one staging slot (caller-chosen index)
 struct Ring {          // one output ring entry (submission order)
     uint8_t *d_out = nullptr;
     uint8_t *h_out = nullptr;
-    uint8_t *d_meta = nullptr;        // map bytes, then the u32 count
+    uint8_t *d_meta = nullptr;        // map bytes, policy bytes, then the u32 count
     uint8_t *h_meta = nullptr;
     cudaEvent_t h2d_start = nullptr, h2d_done = nullptr;
     cudaEvent_t k_start = nullptr, k_done = nullptr;
@@ -71,6 +71,7 @@ struct sk_session {
     Slot slots[kMaxInflight];
     Ring ring[kMaxInflight];
     uint32_t *d_scratch = nullptr;
+    uint32_t *d_state = nullptr;      // per-macroblock temporal policy state
     int32_t *d_voff = nullptr;
     int16_t *d_vtap = nullptr;
     cudaStream_t s_copy = nullptr, s_comp = nullptr, s_d2h = nullptr;
@@ -181,6 +182,7 @@ void free_session(sk_session *s)
         for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     }
     if (s->d_scratch) cudaFree(s->d_scratch);
+    if (s->d_state) cudaFree(s->d_state);
     if (s->d_voff) cudaFree(s->d_voff);
     if (s->d_vtap) cudaFree(s->d_vtap);
     for (cudaEvent_t e : s->mark) if (e) cudaEventDestroy(e);
@@ -201,6 +203,11 @@ int validate(const sk_config &c, std::string &why)
     if (c.matrix < SK_MATRIX_BT601 || c.matrix > SK_MATRIX_BT2020) { why = "unknown matrix"; return SK_ERR_ARG; }
     if (c.chroma_site != SK_SITE_NONE && c.chroma_site != SK_SITE_H_COSITED) { why = "unknown chroma_site"; return SK_ERR_ARG; }
     if (c.n_inflight < 2 || c.n_inflight > kMaxInflight) { why = "n_inflight must be in [2, 8]"; return SK_ERR_ARG; }
+    auto bad_knob = [](int v) { return v < 1 || v > 255; };
+    if (bad_knob(c.damage_block_threshold) || bad_knob(c.damage_block_duration) || bad_knob(c.paint_over_trigger_frames)) {
+        why = "damage_block_threshold, damage_block_duration and paint_over_trigger_frames must be in [1, 255]";
+        return SK_ERR_ARG;
+    }
     const bool scaling = c.in_width != c.out_width || c.in_height != c.out_height;
     if (scaling) {
         if (c.scale_method != SK_SCALE_BILINEAR) { why = "only scale_method bilinear is supported"; return SK_ERR_UNSUPPORTED; }
@@ -230,7 +237,9 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.out = r.d_out;
     f.prev = (s->prev_ring >= 0) ? s->ring[s->prev_ring].d_out : nullptr;
     f.map = r.d_meta;
-    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta + s->map_bytes);
+    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta + 2 * s->map_bytes);
+    f.state = s->d_state;                       // nullptr unless SK_FLAG_POLICY
+    f.policy = r.d_meta + s->map_bytes;
     f.scratch = s->d_scratch;
     f.v_off = s->d_voff;
     f.v_tap = s->d_vtap;
@@ -339,6 +348,9 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     if (c.n_inflight == 0) c.n_inflight = 2;
     if (c.scale_method == 0) c.scale_method = SK_SCALE_BILINEAR;
     if (c.device_id < 0) c.device_id = 0;
+    if (c.damage_block_threshold == 0) c.damage_block_threshold = 10;       // selkies.py:2950
+    if (c.damage_block_duration == 0) c.damage_block_duration = 20;         // selkies.py:2951
+    if (c.paint_over_trigger_frames == 0) c.paint_over_trigger_frames = 15; // selkies.py:2949
     std::string why;
     int rc = validate(c, why);
     if (rc != SK_OK) return fail(nullptr, rc, why);
@@ -401,6 +413,9 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     g.out_fmt = c.out_format;
     g.site = c.chroma_site;
     g.damage = (c.flags & SK_FLAG_NO_DAMAGE) ? 0 : 1;
+    g.pol_threshold = c.damage_block_threshold;
+    g.pol_duration = c.damage_block_duration;
+    g.pol_trigger = c.paint_over_trigger_frames;
     g.scale_h = g.in_w != g.out_w;
     g.scale_v = g.in_h != g.out_h;
     g.h_inc = g.out_w > 1 ? (int32_t)((((int64_t)g.in_w - 1) << 16) / (g.out_w - 1) - 1) : 0;
@@ -409,7 +424,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     g.in_stride = s->d_in_stride;
     s->in_bytes_host = (size_t)c.in_stride * c.in_height;
     s->map_bytes = (size_t)ru(g.mb_w * g.mb_h, 4);
-    s->meta_bytes = s->map_bytes + 4;
+    s->meta_bytes = 2 * s->map_bytes + 4;
 
     SK_TRY(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
     SK_TRY(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
@@ -434,6 +449,10 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     }
     SK_TRY(cudaMalloc((void **)&s->d_scratch, 256));
     SK_TRY(cudaMemset(s->d_scratch, 0, 256));
+    if ((c.flags & SK_FLAG_POLICY) && !(c.flags & SK_FLAG_NO_DAMAGE)) {
+        SK_TRY(cudaMalloc((void **)&s->d_state, s->map_bytes * sizeof(uint32_t)));
+        SK_TRY(cudaMemset(s->d_state, 0, s->map_bytes * sizeof(uint32_t)));
+    }
     for (cudaEvent_t &ev : s->mark) SK_TRY(cudaEventCreate(&ev));
     if (s->scaling) {
         std::vector<int32_t> off;
@@ -573,7 +592,9 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
         if (s->dev != L->dev || a.in_width != b.in_width || a.in_height != b.in_height ||
             a.out_width != b.out_width || a.out_height != b.out_height || a.in_format != b.in_format ||
             a.out_format != b.out_format || a.matrix != b.matrix || a.chroma_site != b.chroma_site ||
-            a.scale_variant != b.scale_variant || ((a.flags ^ b.flags) & SK_FLAG_NO_DAMAGE))
+            a.scale_variant != b.scale_variant || ((a.flags ^ b.flags) & (SK_FLAG_NO_DAMAGE | SK_FLAG_POLICY)) ||
+            a.damage_block_threshold != b.damage_block_threshold || a.damage_block_duration != b.damage_block_duration ||
+            a.paint_over_trigger_frames != b.paint_over_trigger_frames)
             return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
         for (int j = 0; j < i; j++)
             if (ss[j] == s) return fail(L, SK_ERR_STATE, "a session appears twice in one batch");
@@ -655,8 +676,12 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
             out->host_damage_map = r.h_meta;
             out->dev_damage_map = r.d_meta;
             uint32_t cnt;
-            std::memcpy(&cnt, r.h_meta + s->map_bytes, 4);
+            std::memcpy(&cnt, r.h_meta + 2 * s->map_bytes, 4);
             out->damaged_count = cnt;
+            if (s->d_state) {
+                out->host_policy_map = r.h_meta + s->map_bytes;
+                out->dev_policy_map = r.d_meta + s->map_bytes;
+            }
         }
         if (timing && own_events) {
             float ms = 0.f;

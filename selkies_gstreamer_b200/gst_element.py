@@ -110,6 +110,11 @@ def element_class():
     gi.require_version("Gst", "1.0")
     gi.require_version("GstBase", "1.0")
     from gi.repository import GObject, Gst, GstBase
+    try:
+        gi.require_version("GstVideo", "1.0")
+        from gi.repository import GstVideo
+    except (ValueError, ImportError):       # ROI metas / key-unit events need gst-plugins-base's GstVideo
+        GstVideo = None
 
     class B200PreEncode(GstBase.BaseTransform):
         __gstmetadata__ = ("B200 pre-encode stage", "Filter/Converter/Video/Scaler",
@@ -133,6 +138,24 @@ def element_class():
                             GObject.ParamFlags.READWRITE),
             "damage": (GObject.TYPE_BOOLEAN, "damage", "produce the per-16x16 damage map", True,
                        GObject.ParamFlags.READWRITE),
+            "damage-block-threshold": (GObject.TYPE_UINT, "damage-block-threshold",
+                                       "consecutive damaged frames that make a block hot (selkies.py:2950)",
+                                       1, 255, 10, GObject.ParamFlags.READWRITE),
+            "damage-block-duration": (GObject.TYPE_UINT, "damage-block-duration",
+                                      "frames a hot block stays hot after its last change (selkies.py:2951)",
+                                      1, 255, 20, GObject.ParamFlags.READWRITE),
+            "paint-over-trigger-frames": (GObject.TYPE_UINT, "paint-over-trigger-frames",
+                                          "still frames before a changed block is repainted (selkies.py:2949)",
+                                          1, 255, 15, GObject.ParamFlags.READWRITE),
+            "keyframe-damage-fraction": (GObject.TYPE_DOUBLE, "keyframe-damage-fraction",
+                                         "damaged fraction of the frame that requests a key unit", 0.0, 1.0, 0.6,
+                                         GObject.ParamFlags.READWRITE),
+            "roi-meta": (GObject.TYPE_BOOLEAN, "roi-meta", "attach GstVideoRegionOfInterestMeta for damaged / "
+                         "paint-over regions (x264enc honours them)", True, GObject.ParamFlags.READWRITE),
+            "force-keyframes": (GObject.TYPE_BOOLEAN, "force-keyframes", "send downstream force-key-unit when the "
+                                "damaged fraction crosses keyframe-damage-fraction", True, GObject.ParamFlags.READWRITE),
+            "paint-over-delta-qp": (GObject.TYPE_INT, "paint-over-delta-qp", "delta-qp put on paint-over regions",
+                                    -51, 51, -8, GObject.ParamFlags.READWRITE),
             "damaged-blocks": (GObject.TYPE_UINT, "damaged-blocks", "damaged macroblocks in the last frame",
                                0, GObject.G_MAXUINT, 0, GObject.ParamFlags.READABLE),
             "frames": (GObject.TYPE_UINT64, "frames", "frames converted since the last caps change",
@@ -145,12 +168,43 @@ def element_class():
             self.set_qos_enabled(True)      # videoconvert's default; late frames are dropped before transform
             self.set_passthrough(False)
             self.set_in_place(False)
+            self._signalling = {"roi-meta": True, "force-keyframes": True, "paint-over-delta-qp": -8}
+            self._keyunit_count = 0
 
         def do_get_property(self, prop):
+            if prop.name in self._signalling:
+                return self._signalling[prop.name]
             return self.core.get_property(prop.name)
 
         def do_set_property(self, prop, value):
-            self.core.set_property(prop.name, value)
+            if prop.name in self._signalling:
+                self._signalling[prop.name] = value
+            else:
+                self.core.set_property(prop.name, value)
+
+        def apply_decision(self, outbuf, decision):
+            """Turn one frame's decision into what encoders understand: ROI metas on the buffer
+            and, when most of the frame changed, a downstream force-key-unit event."""
+            if decision is None or GstVideo is None:
+                return 0
+            n = 0
+            if self._signalling["roi-meta"]:
+                for r in decision.damage_regions:
+                    GstVideo.buffer_add_video_region_of_interest_meta(outbuf, "damage", r.x, r.y, r.w, r.h)
+                    n += 1
+                for r in decision.paint_over_regions:
+                    meta = GstVideo.buffer_add_video_region_of_interest_meta(outbuf, "paint-over", r.x, r.y, r.w, r.h)
+                    if meta is not None and hasattr(meta, "add_param"):
+                        st = Gst.Structure.new_empty("roi/x264enc")
+                        st.set_value("delta-qp", float(self._signalling["paint-over-delta-qp"]))
+                        meta.add_param(st)
+                    n += 1
+            if self._signalling["force-keyframes"] and decision.force_keyframe and self.core.frames > 1:
+                ev = GstVideo.video_event_new_downstream_force_key_unit(
+                    outbuf.pts, Gst.CLOCK_TIME_NONE, Gst.CLOCK_TIME_NONE, True, self._keyunit_count)
+                self._keyunit_count += 1
+                self.srcpad.push_event(ev)
+            return n
 
         def do_start(self):
             return self.core.start()
@@ -189,6 +243,7 @@ def element_class():
                 self.core.last_error = str(e)
                 rc = _stage.FLOW_ERROR
             if rc == _stage.FLOW_OK:
+                self.apply_decision(outbuf, self.core.last_decision)
                 return Gst.FlowReturn.OK
             # Surfaces as a bus ERROR message, which the reference's bus_call handles (gstwebrtc_app.py:1654-1674).
             Gst.error(f"{FACTORY_NAME}: {self.core.last_error}")

@@ -53,6 +53,7 @@ class FrameResult:
     h2d_us: float
     kernel_us: float
     d2h_us: float
+    policy_map: np.ndarray | None = None   # uint8 [mb_h, mb_w] of SK_POLICY_* bits
 
 
 class PreencodeSession:
@@ -60,7 +61,8 @@ class PreencodeSession:
                  out_width: int | None = None, out_height: int | None = None,
                  colorimetry=None, chroma_site=None, device_id: int = -1, n_inflight: int = 2,
                  in_stride: int = 0, damage: bool = True, host_output: bool = True, timing: bool = False,
-                 scale_variant: int = _abi.SK_SCALE_VARIANT_GST_LQ):
+                 scale_variant: int = _abi.SK_SCALE_VARIANT_GST_LQ, policy: bool = False, damage_block_threshold: int = 0,
+                 damage_block_duration: int = 0, paint_over_trigger_frames: int = 0):
         self._lib = _abi.load()
         self._h = ctypes.c_void_p()
         if in_format.upper() not in IN_FORMATS:
@@ -75,12 +77,13 @@ class PreencodeSession:
         self.in_stride = int(in_stride) or 4 * self.width
         self.n_inflight = n_inflight
         flags = (0 if damage else _abi.SK_FLAG_NO_DAMAGE) | (_abi.SK_FLAG_HOST_OUTPUT if host_output else 0) \
-            | (_abi.SK_FLAG_TIMING if timing else 0)
+            | (_abi.SK_FLAG_TIMING if timing else 0) | (_abi.SK_FLAG_POLICY if policy else 0)
         self.flags = flags
         cfg = _abi.SkConfig(ctypes.sizeof(_abi.SkConfig), device_id, self.width, self.height, self.in_stride,
                             IN_FORMATS[in_format.upper()], self.out_width, self.out_height,
                             OUT_FORMATS[self.out_format], self.matrix, self.site, _abi.SK_SCALE_BILINEAR,
-                            scale_variant, n_inflight, flags)
+                            scale_variant, n_inflight, flags, damage_block_threshold, damage_block_duration,
+                            paint_over_trigger_frames)
         rc = self._lib.sk_session_create(ctypes.byref(cfg), ctypes.byref(self._h))
         if rc != _abi.SK_OK:
             self._h = ctypes.c_void_p()
@@ -164,8 +167,12 @@ class PreencodeSession:
         if r.host_damage_map:
             buf = (ctypes.c_uint8 * (r.mb_w * r.mb_h)).from_address(r.host_damage_map)
             dmap = np.frombuffer(buf, dtype=np.uint8).reshape(r.mb_h, r.mb_w)
+        pmap = None
+        if r.host_policy_map:
+            buf = (ctypes.c_uint8 * (r.mb_w * r.mb_h)).from_address(r.host_policy_map)
+            pmap = np.frombuffer(buf, dtype=np.uint8).reshape(r.mb_h, r.mb_w)
         return FrameResult(r.frame_id, frame, dmap, r.damaged_count, r.dev_frame or 0, r.dev_damage_map or 0,
-                           tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us)
+                           tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us, pmap)
 
     def convert(self, frame: np.ndarray, slot: int = 0, copy: bool = False) -> FrameResult:
         """Synchronous convenience: upload → submit → wait (see wait() about borrowed views)."""
@@ -174,6 +181,7 @@ class PreencodeSession:
         if copy:
             r.frame = None if r.frame is None else r.frame.copy()
             r.damage_map = None if r.damage_map is None else r.damage_map.copy()
+            r.policy_map = None if r.policy_map is None else r.policy_map.copy()
         return r
 
     def reset_history(self):

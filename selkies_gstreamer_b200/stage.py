@@ -25,6 +25,7 @@ import threading
 from fractions import Fraction
 
 from . import _abi, colorimetry as _col
+from .damage_policy import DamagePolicy
 from .session import PreencodeError, PreencodeSession, frame_layout
 
 SINK_FORMATS = ("BGRx", "BGRA", "RGBx", "RGBA")
@@ -194,6 +195,11 @@ class PreEncodeStage:
         "damage": (bool, True, None),
         "n-inflight": (int, 2, lambda v: 2 <= v <= 8),
         "scale-variant": (int, _abi.SK_SCALE_VARIANT_GST_LQ, lambda v: v in (0, 1)),
+        # temporal damage policy knobs (src/selkies/selkies.py:2949-2951)
+        "damage-block-threshold": (int, 10, lambda v: 1 <= v <= 255),
+        "damage-block-duration": (int, 20, lambda v: 1 <= v <= 255),
+        "paint-over-trigger-frames": (int, 15, lambda v: 1 <= v <= 255),
+        "keyframe-damage-fraction": (float, 0.6, lambda v: 0.0 < v <= 1.0),
     }
     READ_ONLY = ("frames", "damaged-blocks", "damaged-fraction", "total-blocks")
 
@@ -208,7 +214,11 @@ class PreEncodeStage:
         self.last_damage_map = None
         self.last_damaged = 0
         self.last_error = ""
-        self.on_damage = None               # callable(stage, map, count): hook for ROI / keyframe policy
+        self.on_damage = None               # callable(stage, map, count): raw hook
+        self.on_decision = None             # callable(stage, FrameDecision): ROI rectangles / keyframe / paint-over
+        self.last_policy_map = None
+        self.last_decision = None
+        self._policy = None
 
     # -- properties ---------------------------------------------------------
     def set_property(self, name: str, value):
@@ -224,6 +234,10 @@ class PreEncodeStage:
         elif typ is int:
             if isinstance(value, bool) or not isinstance(value, int):
                 raise StageError(f"property '{name}' expects an integer")
+        elif typ is float:
+            if isinstance(value, bool) or not isinstance(value, (int, float)):
+                raise StageError(f"property '{name}' expects a number")
+            value = float(value)
         if name == "method" and value == 1:
             value = "bilinear"
         if check and not check(value):
@@ -231,7 +245,10 @@ class PreEncodeStage:
         with self._lock:
             changed = self._props[name] != value
             self._props[name] = value
-            needs_session = name in ("cuda-device-id", "damage", "n-inflight", "scale-variant")
+            needs_session = name in ("cuda-device-id", "damage", "n-inflight", "scale-variant",
+                                     "damage-block-threshold", "damage-block-duration", "paint-over-trigger-frames")
+            if name == "keyframe-damage-fraction" and self._policy is not None:
+                self._policy.keyframe_fraction = value
             if changed and needs_session and self._session is not None:
                 self._recreate_locked()
 
@@ -366,7 +383,11 @@ class PreEncodeStage:
             out_width=o["width"], out_height=o["height"], colorimetry=o.get("colorimetry"),
             chroma_site=o.get("chroma-site"), device_id=self._props["cuda-device-id"],
             n_inflight=self._props["n-inflight"], damage=self._props["damage"], host_output=True,
-            scale_variant=self._props["scale-variant"])
+            scale_variant=self._props["scale-variant"], policy=self._props["damage"],
+            damage_block_threshold=self._props["damage-block-threshold"],
+            damage_block_duration=self._props["damage-block-duration"],
+            paint_over_trigger_frames=self._props["paint-over-trigger-frames"])
+        self._policy = DamagePolicy(o["width"], o["height"], self._props["keyframe-damage-fraction"])
         self.frames = 0
 
     @property
@@ -397,10 +418,16 @@ class PreEncodeStage:
                 r = s.wait(s.submit(slot))
                 ctypes.memmove(out_ptr, r.frame.ctypes.data, s.frame_bytes)
                 self.frames += 1
-                self.last_damage_map = r.damage_map
+                # copies: the session's pinned buffers are reused n_inflight frames later
+                self.last_damage_map = None if r.damage_map is None else r.damage_map.copy()
+                self.last_policy_map = None if r.policy_map is None else r.policy_map.copy()
                 self.last_damaged = r.damaged_count
-                if self.on_damage is not None and r.damage_map is not None:
-                    self.on_damage(self, r.damage_map, r.damaged_count)
+                if r.damage_map is not None:
+                    if self.on_damage is not None:
+                        self.on_damage(self, self.last_damage_map, r.damaged_count)
+                    self.last_decision = self._policy.decide(self.last_damage_map, self.last_policy_map, r.damaged_count)
+                    if self.on_decision is not None:
+                        self.on_decision(self, self.last_decision)
                 return FLOW_OK
             except (StageError, PreencodeError) as e:
                 self.last_error = str(e)
@@ -423,3 +450,5 @@ class PreEncodeStage:
         with self._lock:
             if self._session is not None:
                 self._session.reset_history()
+            if self._policy is not None:
+                self._policy.reset()

@@ -36,9 +36,9 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_version_and_struct_sizes(lib):
     assert lib.sk_version() == _abi.SK_ABI_VERSION
-    assert ctypes.sizeof(_abi.SkConfig) == 15 * 4
+    assert ctypes.sizeof(_abi.SkConfig) == 18 * 4
     # the header's sk_result: u64, 2 ptr, size_t, 3 size_t, 3 i32 (+pad), 2 ptr, 2 i32, u32, 3 float
-    assert ctypes.sizeof(_abi.SkResult) == 8 + 16 + 8 + 24 + 16 + 16 + 8 + 4 + 12
+    assert ctypes.sizeof(_abi.SkResult) == 8 + 16 + 8 + 24 + 16 + 16 + 8 + 4 + 12 + 16
 
 
 def test_header_cites_reference_lines():
@@ -64,6 +64,8 @@ def test_bad_struct_size_is_rejected(lib):
     (dict(n_inflight=1), _abi.SK_ERR_ARG),
     (dict(in_stride=100), _abi.SK_ERR_ARG),
     (dict(out_width=3840, out_height=2160), _abi.SK_ERR_UNSUPPORTED),   # enlarging
+    (dict(damage_block_threshold=300), _abi.SK_ERR_ARG),
+    (dict(paint_over_trigger_frames=-1), _abi.SK_ERR_ARG),
 ])
 def test_config_validation_happens_before_cuda(lib, kw, code):
     base = dict(struct_size=ctypes.sizeof(_abi.SkConfig), device_id=-1, in_width=1920, in_height=1080, in_stride=0,

@@ -11,7 +11,8 @@ import numpy as np
 import pytest
 
 from oracle import cpu_oracle as o
-from selkies_gstreamer_b200 import PreencodeError, PreencodeSession, _abi, batch_submit, launch_count, synth
+from selkies_gstreamer_b200 import (PreencodeError, PreencodeSession, SessionBatch, _abi, batch_submit, launch_count,
+                                   synth)
 
 pytestmark = pytest.mark.gpu
 
@@ -316,6 +317,11 @@ def test_batch_rejects_mixed_configuration():
         a.close(); b.close()
 
 
+def test_policy_map_is_absent_unless_asked_for():
+    with PreencodeSession(64, 64) as s:
+        assert s.convert(rand_frame(64, 64, 1)).policy_map is None
+
+
 def test_timing_fields_are_filled():
     f = rand_frame(1920, 1080, 4)
     with PreencodeSession(1920, 1080, timing=True) as s:
@@ -387,3 +393,66 @@ def test_stage_transform_and_renegotiation():
     # buffers that are too small are flow errors, not crashes
     assert s.transform(f0.ctypes.data, 16, out0.ctypes.data, out0.nbytes) == st.FLOW_ERROR
     assert s.stop()
+
+
+# ---- temporal damage policy (in-kernel counters) ------------------------------------
+@pytest.mark.parametrize("knobs", [(10, 20, 15), (2, 3, 4)])
+@pytest.mark.parametrize("mode", ["convert", "scale"])
+def test_policy_map_matches_oracle_over_a_long_sequence(knobs, mode):
+    w, h = 640, 360
+    ow, oh = (w, h) if mode == "convert" else (480, 270)
+    mbw, mbh = (ow + 15) // 16, (oh + 15) // 16
+    rng = np.random.default_rng(knobs[0])
+    base = synth.desktop(w, h)
+    tracker = o.PolicyTracker(mbw, mbh, *knobs)
+    with PreencodeSession(w, h, out_width=ow, out_height=oh, colorimetry=1, chroma_site=1, policy=True,
+                          damage_block_threshold=knobs[0], damage_block_duration=knobs[1],
+                          paint_over_trigger_frames=knobs[2]) as s:
+        cur = base.copy()
+        seen_hot = seen_paint = False
+        for t in range(70):
+            if t < 14:
+                cur[40:90, 100:260, :3] = rng.integers(0, 256, (50, 160, 3), dtype=np.uint8)   # a video region
+            if t in (3, 30):
+                cur[200:210, 400:420, :3] ^= 0x40                                               # one-off edits
+            if 40 <= t < 44:
+                cur[300:330, 20:60, :3] = rng.integers(0, 256, (30, 40, 3), dtype=np.uint8)
+            r = s.convert(cur, slot=t & 1)
+            want = tracker.update(r.damage_map)
+            assert (r.policy_map == want).all(), f"frame {t}"
+            assert ((r.policy_map & 1) == r.damage_map).all()
+            seen_hot |= bool((r.policy_map & 2).any())
+            seen_paint |= bool((r.policy_map & 4).any())
+        assert seen_hot and seen_paint
+        # a history reset makes everything damaged again but keeps the counters running
+        s.reset_history()
+        r = s.convert(cur, slot=0)
+        assert (r.policy_map == tracker.update(r.damage_map)).all() and r.damage_map.all()
+
+
+def test_policy_in_batched_launches():
+    w, h, n = 640, 360, 3
+    sessions = [PreencodeSession(w, h, colorimetry=1, chroma_site=1, policy=True, damage_block_threshold=2,
+                                 damage_block_duration=3, paint_over_trigger_frames=2) for _ in range(n)]
+    try:
+        frames = [[rand_frame(w, h, 10 * i + k) if k < 2 else None for k in range(2)] for i in range(n)]
+        for s, (a, b) in zip(sessions, frames):
+            s.upload(0, a); s.wait(s.submit(0))
+            s.upload(1, b); s.wait(s.submit(1))
+            s.reset_history()
+        trackers = [o.PolicyTracker(40, 23, 2, 3, 2) for _ in range(n)]
+        for tr in trackers:                       # the two set-up frames already advanced the counters
+            tr.update(np.ones((23, 40), np.uint8)); tr.update(np.ones((23, 40), np.uint8))
+        batch = SessionBatch(sessions)
+        sets = [batch.frame_set([s.device_input(k)[0] for s in sessions]) for k in (0, 1)]
+        stride = sessions[0].device_input(0)[1]
+        order = [0, 1, 1, 1, 1, 1, 0, 0, 0]
+        for fid, k in enumerate(order):
+            batch.submit(sets[k], stride, 500 + fid)
+            batch.wait(500 + fid)
+            for s, tr in zip(sessions, trackers):
+                r = s.wait(500 + fid)
+                assert (r.policy_map == tr.update(r.damage_map)).all(), (fid, k)
+    finally:
+        for s in sessions:
+            s.close()

@@ -179,7 +179,39 @@ def _install_fake_gi(monkeypatch):
     GObject.G_MAXUINT, GObject.G_MAXINT, GObject.G_MAXUINT64 = 2**32 - 1, 2**31 - 1, 2**64 - 1
     GObject.ParamFlags = _Enum(READWRITE=3, READABLE=1)
     GObject.type_register = lambda cls: cls
-    repo.Gst, repo.GstBase, repo.GObject = Gst, GstBase, GObject
+    Gst.CLOCK_TIME_NONE = 2**64 - 1
+
+    class _Structure(dict):
+        @classmethod
+        def new_empty(cls, name):
+            s = cls()
+            s.name = name
+            return s
+
+        def set_value(self, k, v):
+            self[k] = v
+
+    Gst.Structure = _Structure
+
+    class _Meta:
+        def __init__(self, kind, rect):
+            self.kind, self.rect, self.params = kind, rect, []
+
+        def add_param(self, st):
+            self.params.append(st)
+
+    GstVideo = types.ModuleType("GstVideo")
+    GstVideo.metas, GstVideo.events = [], []
+
+    def add_roi(buf, kind, x, y, w, h):
+        m = _Meta(kind, (x, y, w, h))
+        GstVideo.metas.append(m)
+        return m
+
+    GstVideo.buffer_add_video_region_of_interest_meta = add_roi
+    GstVideo.video_event_new_downstream_force_key_unit = lambda *a: ("force-key-unit",) + a
+    GObject.TYPE_DOUBLE = "TYPE_DOUBLE"
+    repo.Gst, repo.GstBase, repo.GObject, repo.GstVideo = Gst, GstBase, GObject, GstVideo
     gi.repository = repo
     for name, mod in (("gi", gi), ("gi.repository", repo)):
         monkeypatch.setitem(sys.modules, name, mod)
@@ -244,3 +276,35 @@ def test_pipeline_patch_swaps_factory_names(monkeypatch):
     assert made == ["b200preencode", "identity", "b200preencode", "x264enc"]
     assert b._e.props == {} and c.props == {"cuda-device-id": 1}
     assert Gst.ElementFactory.make is make
+
+
+def test_gst_adaptor_signals_roi_and_keyframes(monkeypatch):
+    Gst = _install_fake_gi(monkeypatch)
+    from gi.repository import GstVideo
+    from selkies_gstreamer_b200 import gst_element
+    from selkies_gstreamer_b200.damage_policy import FrameDecision, Region
+    monkeypatch.setattr(gst_element, "_element_class", None)
+    el = gst_element.element_class()()
+    pushed = []
+    el.srcpad = types.SimpleNamespace(push_event=pushed.append)
+    outbuf = types.SimpleNamespace(pts=1234)
+    dec = FrameDecision(12, 920, True, False, [Region(80, 32, 64, 32)], [Region(0, 160, 16, 16, "paint-over")], 0.0)
+    el.core.frames = 5
+    assert el.apply_decision(outbuf, dec) == 2
+    kinds = [(m.kind, m.rect) for m in GstVideo.metas]
+    assert kinds == [("damage", (80, 32, 64, 32)), ("paint-over", (0, 160, 16, 16))]
+    assert GstVideo.metas[1].params[0].name == "roi/x264enc" and GstVideo.metas[1].params[0]["delta-qp"] == -8.0
+    assert pushed and pushed[0][0] == "force-key-unit" and pushed[0][1] == 1234
+    # the first frame's keyframe is implicit; switches turn the signalling off
+    el.core.frames = 1
+    pushed.clear()
+    el.apply_decision(outbuf, dec)
+    assert not pushed
+    prop = types.SimpleNamespace
+    el.do_set_property(prop(name="roi-meta"), False)
+    el.do_set_property(prop(name="force-keyframes"), False)
+    el.core.frames = 9
+    assert el.apply_decision(outbuf, dec) == 0 and not pushed
+    el.do_set_property(prop(name="damage-block-threshold"), 4)
+    assert el.do_get_property(prop(name="damage-block-threshold")) == 4
+    assert el.do_get_property(prop(name="roi-meta")) is False
