@@ -316,6 +316,19 @@ def run_b200(args, rank, world, local_rank, dist):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_t = float(t[0])
     e2e_fps = Se * esteps * world / e2e_t
+    # Same pipeline fed from PAGEABLE capture buffers (what a GstBuffer of ximagesrc is) through
+    # sk_submit_host: the driver stages the copy; reported beside the pinned-staging figure.
+    pg_steps = max(3, esteps // 4)
+    pend = []
+    t0 = time.perf_counter()
+    for k in range(pg_steps):
+        ids = [s.submit_host(k & 1, pair[k & 1]) for s, pair in zip(esess, inputs)]
+        for s, i in zip(esess, pend):
+            s.wait(i)
+        pend = ids
+    for s, i in zip(esess, pend):
+        s.wait(i)
+    e2e_pageable_fps = Se * pg_steps / (time.perf_counter() - t0)
     frame_bytes = esess[0].frame_bytes
     # PCIe in isolation (north_star: the copies are reported separately from the HBM roofline):
     # one session, one frame at a time, CUDA events around its H2D and D2H.
@@ -356,7 +369,8 @@ def run_b200(args, rank, world, local_rank, dist):
                 "d2h_bytes_per_step": world * Se * (frame_bytes + meta_bytes), "sessions_per_gpu": Se, "steps": esteps,
                 "h2d_gbs_per_gpu": e2e_fps / world * 4 * W * H / 1e9,
                 "d2h_gbs_per_gpu": e2e_fps / world * (frame_bytes + meta_bytes) / 1e9,
-                "timing": "wall clock between host syncs, max over ranks"},
+                "timing": "wall clock between host syncs, max over ranks",
+                "pageable_input_fps_rank0": e2e_pageable_fps},
         "pcie": pcie,
         "gpu_launches": int(launches),
         "clocks": clocks,

@@ -148,6 +148,19 @@ int sk_upload(sk_session *s, int slot, const void *src, size_t src_stride);
  * pipeline assembled at gstwebrtc_app.py:941-994. */
 int sk_submit(sk_session *s, int slot, uint64_t frame_id);
 
+/* Same, but the H2D copy reads the caller's own frame buffer (rows `stride` apart, 0 = tight)
+ * instead of the staging slot — the GstBuffer of ximagesrc, or its XShm segment
+ * (gstwebrtc_app.py:210-241) — saving the host-side memcpy of sk_upload.  `slot` only names the
+ * device-side input slot.  With memory pinned by sk_host_register (or cudaHostAlloc) the copy is
+ * an asynchronous DMA; pageable memory is staged by the driver.  The buffer must stay valid and
+ * unchanged until sk_wait(frame_id) returns. */
+int sk_submit_host(sk_session *s, int slot, const void *host_ptr, size_t stride, uint64_t frame_id);
+
+/* Pin / unpin a caller-owned capture buffer (e.g. the XShm segment) for sk_submit_host.
+ * Pinning costs milliseconds: do it once per buffer, not per frame. */
+int sk_host_register(void *ptr, size_t bytes);
+int sk_host_unregister(void *ptr);
+
 /* Same, for a frame that is already in HBM (video/x-raw(memory:CUDAMemory)
  * input, gstwebrtc_app.py:281-284, and the device-resident benchmark).
  * dptr and stride must be 16-byte aligned. */

@@ -9,7 +9,7 @@ src/selkies/legacy/gstwebrtc_app.py:611 / :263-270 of the reference.
 from . import _abi
 from ._abi import PreencodeLibraryError
 from .session import (FrameResult, PreencodeError, PreencodeSession, SessionBatch, batch_submit, device_count,
-                      frame_layout, launch_count)
+                      frame_layout, host_register, host_unregister, launch_count)
 
 __all__ = ["PreencodeSession", "PreencodeError", "PreencodeLibraryError", "FrameResult", "SessionBatch", "batch_submit",
-           "device_count", "frame_layout", "launch_count"]
+           "device_count", "frame_layout", "host_register", "host_unregister", "launch_count"]

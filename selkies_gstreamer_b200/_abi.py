@@ -30,7 +30,7 @@ SK_NOALLOC_MAX_OUT_HEIGHT = 4320
 # Every symbol include/selkies_preencode.h declares (tests check the .so exports all of them).
 EXPORTS = (
     "sk_session_create", "sk_session_destroy", "sk_get_input_staging", "sk_get_device_input",
-    "sk_upload", "sk_submit", "sk_submit_device", "sk_wait", "sk_reset_history",
+    "sk_upload", "sk_submit", "sk_submit_host", "sk_host_register", "sk_host_unregister", "sk_submit_device", "sk_wait", "sk_reset_history",
     "sk_batch_submit", "sk_batch_wait", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
     "sk_scale_frame_noalloc", "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
 )
@@ -113,6 +113,9 @@ def load() -> ctypes.CDLL:
         "sk_get_device_input": (i, [vp, i, vpp, ctypes.POINTER(sz)]),
         "sk_upload": (i, [vp, i, vp, sz]),
         "sk_submit": (i, [vp, i, u64]),
+        "sk_submit_host": (i, [vp, i, vp, sz, u64]),
+        "sk_host_register": (i, [vp, sz]),
+        "sk_host_unregister": (i, [vp]),
         "sk_submit_device": (i, [vp, vp, sz, u64]),
         "sk_wait": (i, [vp, u64, ctypes.POINTER(SkResult)]),
         "sk_reset_history": (i, [vp]),

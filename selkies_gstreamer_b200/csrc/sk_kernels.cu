@@ -35,22 +35,22 @@ __device__ __forceinline__ uint32_t dp4a_us(uint32_t a, uint32_t b, int c)
 // ---- loads -----------------------------------------------------------------
 template <int HINT> __device__ __forceinline__ uint4 ld16(const void *p)
 {
-    if (HINT == 1) return __ldcs(reinterpret_cast<const uint4 *>(p));
+    if (HINT & 1) return __ldcs(reinterpret_cast<const uint4 *>(p));
     return __ldg(reinterpret_cast<const uint4 *>(p));
 }
 template <int HINT> __device__ __forceinline__ uint2 ld8(const void *p)
 {
-    if (HINT == 1) return __ldcs(reinterpret_cast<const uint2 *>(p));
+    if (HINT & 1) return __ldcs(reinterpret_cast<const uint2 *>(p));
     return __ldg(reinterpret_cast<const uint2 *>(p));
 }
 template <int HINT> __device__ __forceinline__ uint32_t ld4(const void *p)
 {
-    if (HINT == 1) return __ldcs(reinterpret_cast<const uint32_t *>(p));
+    if (HINT & 1) return __ldcs(reinterpret_cast<const uint32_t *>(p));
     return __ldg(reinterpret_cast<const uint32_t *>(p));
 }
 template <int HINT> __device__ __forceinline__ uint32_t ld2(const void *p)
 {
-    if (HINT == 1) return __ldcs(reinterpret_cast<const unsigned short *>(p));
+    if (HINT & 1) return __ldcs(reinterpret_cast<const unsigned short *>(p));
     return __ldg(reinterpret_cast<const unsigned short *>(p));
 }
 __device__ __forceinline__ uint32_t ld1(const void *p)
@@ -75,6 +75,12 @@ template <int HINT> __device__ __forceinline__ uint32_t load_word(const uint8_t 
     if (nv == 4) return ld4<HINT>(p);
     if (nv == 2) return ld2<HINT>(p);
     return 0;
+}
+// HINT bit 1 (values 2, 3): streaming (evict-first) stores for the interior path
+template <int HINT> __device__ __forceinline__ void st4(uint8_t *p, uint32_t w)
+{
+    if (HINT & 2) __stcs(reinterpret_cast<uint32_t *>(p), w);
+    else *reinterpret_cast<uint32_t *>(p) = w;
 }
 __device__ __forceinline__ void store_word(uint8_t *p, uint32_t w, int nv)
 {
@@ -292,7 +298,7 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
                     if (lane == 0) left = wrap;
                 }
                 chroma_h<SITE>(uvq[q], left, x, w, hh[rr][q][0], hh[rr][q][1]);
-                if (FULL) *reinterpret_cast<uint32_t *>(orow + q * 128) = yw[q];
+                if (FULL) st4<HINT>(orow + q * 128, yw[q]);
                 else if (rv) store_word(orow + q * 128, yw[q], nvq[q]);
                 if (DAMAGE && rv) {
                     if (FULL) diff[q] |= yw[q] ^ py[r][q];
@@ -308,7 +314,7 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
             const int nv = rv ? nvq[q] : 0;
             if (FMT == 0) {
                 uint8_t *p = f.out + g.off_c0 + o + q * 128;
-                if (FULL) *reinterpret_cast<uint32_t *>(p) = cw;
+                if (FULL) st4<HINT>(p, cw);
                 else store_word(p, cw, nv);
                 if (DAMAGE && rv) diff[q] |= (cw ^ pc[rp][q]) & ((FULL || nvq[q] == 4) ? 0xffffffffu : 0x0000ffffu);
             } else {
@@ -844,8 +850,8 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
     case 9: return launch_convert_shape<4, 2, 0>(g, b, n, st);
     case 10: return launch_convert_shape<2, 4, 0>(g, b, n, st);
     case 11: return launch_convert_shape<1, 4, 0>(g, b, n, st);
-    case 12: return launch_convert_shape<4, 2, 1>(g, b, n, st);
-    case 13: return launch_convert_shape<2, 4, 1>(g, b, n, st);
+    case 12: return launch_convert_shape<1, 2, 2>(g, b, n, st);   // default shape, streaming stores
+    case 13: return launch_convert_shape<1, 2, 3>(g, b, n, st);   // default shape, streaming loads + stores
     }
 }
 

@@ -564,6 +564,55 @@ int sk_submit(sk_session *s, int slot, uint64_t frame_id)
     return submit_common(s, s->geom, sl.d_in, slot, frame_id);
 }
 
+int sk_submit_host(sk_session *s, int slot, const void *host_ptr, size_t stride, uint64_t frame_id)
+{
+    if (!s || !host_ptr) return SK_ERR_ARG;
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    const size_t row = (size_t)4 * s->cfg.in_width;
+    if (stride == 0) stride = row;
+    if (stride < row) return fail(s, SK_ERR_ARG, "stride smaller than a row");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    Slot &sl = s->slots[slot];
+    Ring &r = s->ring[s->seq % (uint64_t)s->n];
+    if (sl.consumed_valid) SK_CUDA(s, cudaStreamWaitEvent(s->s_copy, sl.consumed, 0));
+    if (timing) SK_CUDA(s, cudaEventRecord(r.h2d_start, s->s_copy));
+    // Straight from the caller's buffer into the device slot: no trip through the pinned staging.
+    // Pinned / registered memory is DMA'd asynchronously; pageable memory is staged by the driver
+    // before this returns.  Either way the buffer must stay valid until sk_wait(frame_id) returns.
+    if (stride == (size_t)s->d_in_stride) {
+        SK_CUDA(s, cudaMemcpyAsync(sl.d_in, host_ptr, stride * (size_t)(s->cfg.in_height - 1) + row,
+                                   cudaMemcpyHostToDevice, s->s_copy));
+    } else {
+        SK_CUDA(s, cudaMemcpy2DAsync(sl.d_in, s->d_in_stride, host_ptr, stride, row, s->cfg.in_height,
+                                     cudaMemcpyHostToDevice, s->s_copy));
+    }
+    SK_CUDA(s, cudaEventRecord(r.h2d_done, s->s_copy));
+    return submit_common(s, s->geom, sl.d_in, slot, frame_id);
+}
+
+int sk_host_register(void *ptr, size_t bytes)
+{
+    if (!ptr || !bytes) return SK_ERR_ARG;
+    cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(nullptr, SK_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e));
+    }
+    return SK_OK;
+}
+
+int sk_host_unregister(void *ptr)
+{
+    if (!ptr) return SK_ERR_ARG;
+    cudaError_t e = cudaHostUnregister(ptr);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(nullptr, SK_ERR_CUDA, std::string("cudaHostUnregister: ") + cudaGetErrorString(e));
+    }
+    return SK_OK;
+}
+
 int sk_submit_device(sk_session *s, const void *dptr, size_t stride, uint64_t frame_id)
 {
     if (!s || !dptr) return SK_ERR_ARG;

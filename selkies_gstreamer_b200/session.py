@@ -143,6 +143,19 @@ class PreencodeSession:
         self._check(self._lib.sk_submit(self._h, slot, fid))
         return fid
 
+    def submit_host(self, slot: int, frame, stride: int = 0, frame_id: int | None = None) -> int:
+        """H2D straight from `frame` (numpy [H, W, 4] uint8 or a raw address) — no staging memcpy.
+        The buffer must stay alive and unchanged until wait(frame_id) returns."""
+        if isinstance(frame, np.ndarray):
+            if frame.dtype != np.uint8 or frame.shape != (self.height, self.width, 4) or frame.strides[1:] != (4, 1):
+                raise ValueError("expected a uint8 [H, W, 4] array with contiguous pixels")
+            ptr, stride = frame.ctypes.data, frame.strides[0]
+        else:
+            ptr = int(frame)
+        fid = self._take_id(frame_id)
+        self._check(self._lib.sk_submit_host(self._h, slot, ctypes.c_void_p(ptr), stride, fid))
+        return fid
+
     def submit_device(self, dptr: int, stride: int = 0, frame_id: int | None = None) -> int:
         fid = self._take_id(frame_id)
         self._check(self._lib.sk_submit_device(self._h, ctypes.c_void_p(dptr), stride, fid))
@@ -263,6 +276,21 @@ class SessionBatch:
         if rc != _abi.SK_OK:
             raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
         return list(self._counts)
+
+
+def host_register(array: np.ndarray):
+    """Pin a caller-owned numpy buffer (a capture segment) for submit_host. Undo with host_unregister."""
+    lib = _abi.load()
+    rc = lib.sk_host_register(ctypes.c_void_p(array.ctypes.data), array.nbytes)
+    if rc != _abi.SK_OK:
+        raise PreencodeError(rc, (lib.sk_last_error(None) or b"").decode())
+
+
+def host_unregister(array: np.ndarray):
+    lib = _abi.load()
+    rc = lib.sk_host_unregister(ctypes.c_void_p(array.ctypes.data))
+    if rc != _abi.SK_OK:
+        raise PreencodeError(rc, (lib.sk_last_error(None) or b"").decode())
 
 
 def launch_count() -> int:

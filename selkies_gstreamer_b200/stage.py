@@ -414,8 +414,8 @@ class PreEncodeStage:
                 if out_size < s.frame_bytes:
                     raise StageError(f"output buffer too small: {out_size} < {s.frame_bytes}")
                 slot = self.frames % s.n_inflight
-                s._check(s._lib.sk_upload(s.handle, slot, ctypes.c_void_p(in_ptr), stride))
-                r = s.wait(s.submit(slot))
+                # H2D straight from the mapped input buffer; it stays mapped until wait() returns
+                r = s.wait(s.submit_host(slot, in_ptr, stride))
                 ctypes.memmove(out_ptr, r.frame.ctypes.data, s.frame_bytes)
                 self.frames += 1
                 # copies: the session's pinned buffers are reused n_inflight frames later

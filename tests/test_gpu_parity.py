@@ -165,6 +165,27 @@ def test_strided_capture_rows():
         assert (r.frame == o.convert(np.ascontiguousarray(view), matrix=s.matrix, chroma_site=s.site, n_threads=2)).all()
 
 
+def test_submit_host_pageable_strided_and_registered():
+    from selkies_gstreamer_b200 import host_register, host_unregister
+    big = rand_frame(700, 400, 21)
+    view = big[20:380, 30:670]                                  # 640x360 window of a larger framebuffer (pageable)
+    f2 = np.ascontiguousarray(synth.mutate(np.ascontiguousarray(view), 0.03, seed=5, aligned=False))
+    with PreencodeSession(640, 360, colorimetry=1, chroma_site=1) as s:
+        r0 = s.wait(s.submit_host(0, view))
+        e0 = o.convert(np.ascontiguousarray(view), n_threads=2)
+        assert (r0.frame == e0).all() and r0.damage_map.all()
+        host_register(f2)
+        try:
+            r1 = s.wait(s.submit_host(1, f2))
+            e1 = o.convert(f2, n_threads=2)
+            em, en = o.damage(640, 360, 0, e1, e0)
+            assert (r1.frame == e1).all() and (r1.damage_map == em).all() and r1.damaged_count == en
+        finally:
+            host_unregister(f2)
+        with pytest.raises(ValueError):
+            s.submit_host(0, view[:, :, ::-1])
+
+
 def test_idempotence_and_reset_history():
     f = synth.desktop(1920, 1080)
     with PreencodeSession(1920, 1080, n_inflight=3) as s:
