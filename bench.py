@@ -203,6 +203,8 @@ def run_b200(args, rank, world, local_rank, dist):
         raise SystemExit(f"rank {rank}: CUDA device {local_rank} not available — the product path has no fallback")
     if args.variant is not None:
         lib.sk_set_kernel_variant(args.variant)
+    if args.no_snake:
+        lib.sk_set_kernel_variant(102)
     S = args.sessions
     inputs = make_inputs(S, rank)
 
@@ -395,6 +397,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=40)
     ap.add_argument("--variant", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-snake", action="store_true", help="tuning: do not alternate the traversal direction per launch")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 

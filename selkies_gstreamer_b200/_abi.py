@@ -10,7 +10,8 @@ import os
 import subprocess
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "libselkies_preencode.so")
+# SELKIES_PREENCODE_LIB selects another build of the same library (A/B measurements); never a fallback.
+LIB_PATH = os.environ.get("SELKIES_PREENCODE_LIB") or os.path.join(_PKG, "libselkies_preencode.so")
 CSRC = os.path.join(_PKG, "csrc")
 
 SK_OK = 0

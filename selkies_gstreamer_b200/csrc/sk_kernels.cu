@@ -219,19 +219,8 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
     const uint8_t *in = f.in + in_off;
     const bool want_halo = SITE == 1 && lane == 0 && bx0 > 0;
 
-    // ---- phase 1: issue every load of this thread up front
-#pragma unroll
-    for (int r = 0; r < ROWS; r++) {
-        const bool rv = FULL || (y0 + r) < h;
-        const uint8_t *row = in + (uint32_t)r * (uint32_t)g.in_stride;
-#pragma unroll
-        for (int q = 0; q < QX; q++) {
-            if (FULL) px[r][q] = ld16<HINT>(row + q * 512);
-            else px[r][q] = load_quad<HINT>(row + q * 512, rv ? nvq[q] : 0);
-        }
-        halo[r] = 0;
-        if (want_halo && rv) halo[r] = ld4<0>(row - 4);   // lane 0: pixel left of the warp
-    }
+    // ---- phase 1: issue every load of this thread up front; the narrow previous-frame loads go
+    //      first so that ptxas keeps all of them ahead of the first dependent instruction
     if (DAMAGE) {
         const uint8_t *pyb = f.prev + y_off;
 #pragma unroll
@@ -267,6 +256,18 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
         }
     }
 
+#pragma unroll
+    for (int r = 0; r < ROWS; r++) {
+        const bool rv = FULL || (y0 + r) < h;
+        const uint8_t *row = in + (uint32_t)r * (uint32_t)g.in_stride;
+#pragma unroll
+        for (int q = 0; q < QX; q++) {
+            if (FULL) px[r][q] = ld16<HINT>(row + q * 512);
+            else px[r][q] = load_quad<HINT>(row + q * 512, rv ? nvq[q] : 0);
+        }
+        halo[r] = 0;
+        if (want_halo && rv) halo[r] = ld4<0>(row - 4);   // lane 0: pixel left of the warp
+    }
     // ---- phase 2: arithmetic, stores, compare
     uint8_t *oy = f.out + y_off;
 #pragma unroll
@@ -335,26 +336,32 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
 
 // Register budget: RP*QX <= 2 must stay at 5 CTAs/SM (<= 48 registers) — the sweep in profiles/ shows the
 // occupancy cliff costs ~12 % of the HBM rate.
-template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT>
+template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT, bool POLICY>
 __global__ void __launch_bounds__(kThreads, (RP * QX <= 2) ? 5 : 1)
 sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
 {
     constexpr int ROWS = 2 * RP;
     constexpr int NMB = RP * QX * 8;      // macroblocks per CTA
-    const SkFrame &f = batch.f[blockIdx.z];
+    // Launches alternate the traversal direction (g.reverse): what the previous launch wrote last —
+    // the "previous frame" of the sessions / rows it finished with — is still in the 126 MB L2 and is
+    // read first by this one.
+    const unsigned bix = g.reverse ? gridDim.x - 1 - blockIdx.x : blockIdx.x;
+    const unsigned biy = g.reverse ? gridDim.y - 1 - blockIdx.y : blockIdx.y;
+    const unsigned biz = g.reverse ? gridDim.z - 1 - blockIdx.z : blockIdx.z;
+    const SkFrame &f = batch.f[biz];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int bx0 = blockIdx.x * (128 * QX);
-    const int by0 = blockIdx.y * (16 * RP);
+    const int bx0 = bix * (128 * QX);
+    const int by0 = biy * (16 * RP);
     const int y0 = by0 + warp * ROWS;
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 * QX <= g.out_w) && (by0 + 16 * RP <= g.out_h);
 
     uint32_t pol_state = 0;
-    if (DAMAGE) {
+    if (DAMAGE && POLICY) {
         const int t = threadIdx.x;
-        pol_state = policy_prefetch(f, g, t < NMB, blockIdx.x * (8 * QX) + ((t % (QX * 8)) / 8) * 8 + t % 8,
-                                    blockIdx.y * RP + t / (QX * 8));
+        pol_state = policy_prefetch(f, g, t < NMB, bix * (8 * QX) + ((t % (QX * 8)) / 8) * 8 + t % 8,
+                                    biy * RP + t / (QX * 8));
     }
     uint32_t diff[QX];
     int nvq[QX];
@@ -384,11 +391,11 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
             for (int k = 0; k < WPM; k++)
                 acc |= s_mask[mbrow * WPM + k][q];
             const bool flag = ((acc >> (4 * m)) & 0xfu) != 0;
-            const int bx = blockIdx.x * (8 * QX) + q * 8 + m;
-            const int by = blockIdx.y * RP + mbrow;
+            const int bx = bix * (8 * QX) + q * 8 + m;
+            const int by = biy * RP + mbrow;
             if (bx < g.mb_w && by < g.mb_h) {
                 f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
-                policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
+                if (POLICY) policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
                 hit = flag;
             }
         }
@@ -819,10 +826,12 @@ cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaS
 {
     dim3 grid((g.out_w + 128 * QX - 1) / (128 * QX), (g.out_h + 16 * RP - 1) / (16 * RP), n);
     dim3 block(kThreads);
-#define SK_CASE(FMT, SITE, DMG)                                                             \
-    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                      \
-        sk_convert_kernel<RP, QX, FMT, SITE, DMG, HINT><<<grid, block, 0, st>>>(g, b);      \
-        return cudaGetLastError();                                                         \
+    const bool policy = g.damage != 0 && b.f[0].state != nullptr;
+#define SK_CASE(FMT, SITE, DMG)                                                                    \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                             \
+        if (DMG && policy) sk_convert_kernel<RP, QX, FMT, SITE, DMG, HINT, DMG><<<grid, block, 0, st>>>(g, b);   \
+        else sk_convert_kernel<RP, QX, FMT, SITE, DMG, HINT, false><<<grid, block, 0, st>>>(g, b);  \
+        return cudaGetLastError();                                                                \
     }
     SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
     SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)

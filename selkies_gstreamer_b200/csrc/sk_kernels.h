@@ -27,6 +27,7 @@ struct SkGeom {
     int scale_raw_stride;     // tiled kernel: words per staged raw row (widest tile window, 16-byte chunks)
     // temporal damage policy (per-macroblock saturating counters updated in the same kernel)
     int pol_threshold, pol_duration, pol_trigger;
+    int reverse;              // 1: walk sessions / tiles back to front (alternates per launch, for L2 reuse)
 };
 
 // Per-session pointers of one launch (all device memory).

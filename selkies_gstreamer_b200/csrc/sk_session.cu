@@ -27,6 +27,7 @@ namespace {
 constexpr int kMaxInflight = 8;
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_variant{0};
+std::atomic<int> g_snake{1};            // alternate traversal direction per launch (102 off / 103 on)
 std::atomic<int> g_scale_generic{0};   // tuning/testing: force the generic scale kernel
 thread_local std::string g_create_error;
 
@@ -250,10 +251,12 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     return ri;
 }
 
-cudaError_t launch(const sk_session *s, const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
+cudaError_t launch(const sk_session *s, const SkGeom &g_in, const SkBatch &b, int n, cudaStream_t st)
 {
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    if (s->scaling) return sk_launch_scale(g, b, n, st, g_variant.load());
+    if (s->scaling) return sk_launch_scale(g_in, b, n, st, g_variant.load());
+    SkGeom g = g_in;
+    g.reverse = (int)(s->seq & 1) && g_snake.load();     // seq was advanced by stage_frame: alternates per frame
     return sk_launch_convert(g, b, n, st, g_variant.load());
 }
 
@@ -314,6 +317,10 @@ uint64_t sk_launch_count(void) { return g_launches.load(); }
 
 int sk_set_kernel_variant(int variant)
 {
+    if (variant == 102 || variant == 103) {
+        g_snake.store(variant == 103 ? 1 : 0);
+        return SK_OK;
+    }
     if (variant == 100 || variant == 101) {     // 100: force the generic scale kernel for new sessions; 101: default
         g_scale_generic.store(variant == 100 ? 1 : 0);
         return SK_OK;
