@@ -177,7 +177,9 @@ int sk_reset_history(sk_session *s);
 /* One launch over n sessions of identical configuration on the same device
  * (throughput mode: independent desktop sessions, gstwebrtc_app.py:264-272
  * pins each to a GPU).  dptrs[i] is session i's frame in HBM (stride as in
- * sk_submit_device); all get frame_id.  Completion via sk_wait on each. */
+ * sk_submit_device); all get frame_id.  Completion via sk_wait on each (or sk_batch_wait).
+ * The members share the first session's streams and completion event: destroy the sessions of a
+ * batch together, after the last batch has been waited for. */
 int sk_batch_submit(sk_session **sessions, int n, const void *const *dptrs,
                     size_t stride, uint64_t frame_id);
 
