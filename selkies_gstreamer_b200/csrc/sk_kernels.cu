@@ -596,7 +596,7 @@ __device__ __forceinline__ void cp_async_commit_wait()
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
 }
 
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, bool FULL>
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
                                            const int bx0, const int by0, const int lane, const int warp,
                                            const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out)
@@ -645,7 +645,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     }
 
     // ---- stage: the raw source window of this tile, global -> shared with cp.async (no registers,
-    //      so many CTAs per SM keep their copies in flight while others compute)
+    //      so many CTAs per SM keep their copies in flight while others compute).  Warp w takes
+    //      window rows w, w+8, ... (at most RPW of them), lane l the 16-byte chunks l, l+32, l+64.
     const int xo_first = bx0 > 0 ? bx0 - 1 : 0;                       // halo column included
     const int xo_last = FULL ? bx0 + 127 : min(bx0 + 127, w - 1);
     int xs_first = xo_first, xs_last = xo_last;
@@ -654,17 +655,25 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
         xs_last = ((xo_last * g.h_inc) >> 16) + 1;
     }
     const int cx0 = xs_first & ~3;                                    // 16-byte aligned start
-    const int nch = ((xs_last - cx0) >> 2) + 1;
-    const uint32_t RS = (uint32_t)g.scale_raw_stride;                 // words per raw row
+    const int nch = ((xs_last - cx0) >> 2) + 1;                       // <= 96 (host-checked)
+    const uint32_t RSB = 4u * (uint32_t)g.scale_raw_stride;           // bytes per raw row
     {
-        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0;
-        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW);
-        for (int r = warp; r < nr; r += 8) {
-            const uint8_t *row = base + (size_t)r * (size_t)g.in_stride;
-            for (int c = lane; c < nch; c += 32) {
-                const uint32_t dst = raw_s + 4u * ((uint32_t)r * RS + 4u * (uint32_t)c);
-                if (cx0 + 4 * c + 4 <= g.in_w) cp_async16(dst, row + 16 * c);
-                else cp_async8(dst, row + 16 * c);     // in_w is even: a row may end in a 2-pixel chunk
+        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0 + 16 * lane;
+        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + 16u * (uint32_t)lane;
+        const int rem_px = g.in_w - cx0 - 4 * lane;      // pixels from this lane's first chunk to the row end
+#pragma unroll
+        for (int i = 0; i < RPW; i++) {
+            const int r = warp + 8 * i;
+            if (r < nr) {                                 // warp-uniform
+                const uint8_t *row = base + (size_t)r * (size_t)g.in_stride;
+                const uint32_t dst = raw_s + (uint32_t)r * RSB;
+#pragma unroll
+                for (int j = 0; j < 3; j++) {
+                    if (lane + 32 * j < nch) {
+                        if (rem_px - 128 * j >= 4) cp_async16(dst + 512 * j, row + 512 * j);
+                        else cp_async8(dst + 512 * j, row + 512 * j);
+                    }
+                }
             }
         }
         cp_async_commit_wait();
@@ -674,36 +683,46 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     // ---- pass A: h-scale (or copy) the window once into the second shared buffer; lanes own
     //      adjacent output columns, so the gathers are (nearly) bank-conflict free
     {
-        uint32_t rel[4], fr[4];
-        bool cv[4];
+        uint32_t rel4[4], fr[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             const int xo = bx0 + lane + 32 * k;
-            cv[k] = FULL || xo < w;
-            const int xc = cv[k] ? xo : xo_last;
-            rel[k] = (uint32_t)(xc - cx0);
+            const int xc = (FULL || xo < w) ? xo : xo_last;
+            rel4[k] = 4u * (uint32_t)(xc - cx0);
             fr[k] = 0;
             if (SH) {
                 const int32_t acc = xc * g.h_inc;
-                rel[k] = (uint32_t)((acc >> 16) - cx0);
+                rel4[k] = 4u * (uint32_t)((acc >> 16) - cx0);
                 fr[k] = (uint32_t)(acc >> 8) & 0xffu;
             }
         }
         const bool want_halo = SITE == 1 && lane == 0 && bx0 > 0;
-        uint32_t hrel = (uint32_t)(xo_first - cx0), hf = 0;
+        uint32_t hrel4 = 4u * (uint32_t)(xo_first - cx0), hf = 0;
         if (SH) {
             const int32_t acc = xo_first * g.h_inc;
-            hrel = (uint32_t)((acc >> 16) - cx0);
+            hrel4 = 4u * (uint32_t)((acc >> 16) - cx0);
             hf = (uint32_t)(acc >> 8) & 0xffu;
         }
-        for (int r = warp; r < nr; r += 8) {
-            const uint32_t *R = RAW + (uint32_t)r * RS;
+        const uint8_t *rawb = reinterpret_cast<const uint8_t *>(RAW);
 #pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const uint32_t a = R[rel[k]];
-                S[r][lane + 32 * k] = SH ? lerp_h2(a, R[rel[k] + 1], fr[k]) : a;
+        for (int i = 0; i < RPW; i++) {
+            const int r = warp + 8 * i;
+            if (r < nr) {                                 // warp-uniform
+                const uint8_t *R = rawb + (uint32_t)r * RSB;
+                uint32_t *Srow = &S[r][lane];
+                uint32_t a[4], b[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    a[k] = *reinterpret_cast<const uint32_t *>(R + rel4[k]);
+                    b[k] = SH ? *reinterpret_cast<const uint32_t *>(R + rel4[k] + 4) : 0u;
+                }
+#pragma unroll
+                for (int k = 0; k < 4; k++) Srow[32 * k] = SH ? lerp_h2(a[k], b[k], fr[k]) : a[k];
+                if (want_halo) {
+                    const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
+                    S[r][128] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
+                }
             }
-            if (want_halo) S[r][128] = SH ? lerp_h2(R[hrel], R[hrel + 1], hf) : R[hrel];
         }
     }
     __syncthreads();
@@ -775,8 +794,9 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     }
 }
 
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV>
-__global__ void __launch_bounds__(kThreads, 6)
+// RPW = window rows per warp: 3 (window <= 24 rows, vertical ratio <= 1.375) or 5 (<= 40 rows, ratio <= 2.3)
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW>
+__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : 3)
 sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
 {
     extern __shared__ __align__(16) uint32_t sk_smem[];
@@ -794,8 +814,8 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     uint32_t diff = 0;
     int nvx = 0;
     bool rows_valid = false;
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[8];
@@ -873,10 +893,17 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream
 #define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
         (g.scale_v != 0) == SV) {                                                                     \
-        auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV>;                                    \
-        if (smem > 48 * 1024)                                                                         \
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);       \
-        kern<<<grid, block, smem, st>>>(g, b);                                                        \
+        if (g.scale_rows <= 24) {                                                                     \
+            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 3>;                             \
+            if (smem > 48 * 1024)                                                                     \
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
+            kern<<<grid, block, smem, st>>>(g, b);                                                    \
+        } else {                                                                                      \
+            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 5>;                             \
+            if (smem > 48 * 1024)                                                                     \
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
+            kern<<<grid, block, smem, st>>>(g, b);                                                    \
+        }                                                                                             \
         return cudaGetLastError();                                                                    \
     }
 #define SK_TILED_MODES(FMT, SITE, DMG) \

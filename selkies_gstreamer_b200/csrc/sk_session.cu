@@ -495,7 +495,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         g.scale_raw_stride = 4 * max_chunks;
         const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
-        g.scale_fast = (order_ok && smem <= 96 * 1024 && g_scale_generic.load() == 0) ? 1 : 0;
+        g.scale_fast = (order_ok && max_rows <= 40 && max_chunks <= 96 && smem <= 96 * 1024 &&
+                        g_scale_generic.load() == 0) ? 1 : 0;
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
