@@ -81,9 +81,10 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append([time.perf_counter()] + [c.strip() for c in line.split(",")])
 
-    def stop(self):
+    def stop(self, t_begin=None, t_end=None):
+        """Summary of the samples; t_begin/t_end (perf_counter) mark the timed region inside the sampled span."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -92,18 +93,21 @@ class ClockSampler:
             self.proc.wait(timeout=2)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        sm, mx, reasons, inside = [], [], set(), 0
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
             try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
+                sm.append(float(r[1])); mx.append(float(r[2]))
             except (ValueError, IndexError):
                 continue
-            for n, v in zip(names, r[3:7]):
+            if t_begin is not None and t_begin <= r[0] <= t_end + 0.06:
+                inside += 1
+            for n, v in zip(names, r[4:8]):
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "samples_in_timed_region": inside, "reasons": sorted(reasons),
+                "span": "timed region, plus the same step repeated untimed when the region is shorter than 0.4 s"}
 
 
 # ----------------------------------------------------------------------------- CPU arm
@@ -254,7 +258,13 @@ def run_b200(args, rank, world, local_rank, dist):
     kernel_us.append(leader.last_kernel_us())
     dev_us = leader.marker_elapsed_us()
     launches = sk.launch_count() - launches0
-    clocks = sampler.stop()
+    t_end = time.perf_counter()
+    k = args.steps + args.warmup
+    while time.perf_counter() - t0 < 0.4:      # nvidia-smi samples every 50 ms: keep the same load up, untimed
+        step(k)
+        k += 1
+    sync_all()
+    clocks = sampler.stop(t0, t_end)
     # last result sanity: ~5 % of blocks damaged, never 0 and never all
     r = sess[1].wait(fid - 1)
     nblk = r.damage_map.size
