@@ -184,6 +184,31 @@ __device__ __forceinline__ uint32_t policy_prefetch(const SkFrame &f, const SkGe
     return f.state[(size_t)by * g.mb_w + bx];
 }
 
+// ---- bulk-copy (TMA engine) helpers: 1-D cp.async.bulk global -> shared, completion on an mbarrier
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t done = 0;
+    for (int spin = 0; spin < (1 << 24) && !done; spin++) {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                     "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    }
+    if (!done) __trap();        // never hang the GPU on a protocol error
+}
+
 // ---- no-scale kernel ----------------------------------------------------------
 // CTA = 8 warps.  A warp covers 128*QX pixels of 2*RP rows; lane l owns the
 // quads at x = bx0 + q*128 + 4*l.  The CTA covers 16*RP rows = RP macroblock
@@ -194,9 +219,12 @@ __device__ __forceinline__ uint32_t policy_prefetch(const SkFrame &f, const SkGe
 template <int RP, int QX, int FMT, int SITE, bool DAMAGE, int HINT, bool FULL>
 __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, const int bx0, const int y0,
                                              const int lane, const bool have_prev,
-                                             uint32_t (&diff)[QX], int (&nvq)[QX])
+                                             uint32_t (&diff)[QX], int (&nvq)[QX],
+                                             const uint8_t *tile = nullptr, uint32_t bar = 0, int warp = 0)
 {
     constexpr int ROWS = 2 * RP;
+    constexpr bool BULK = HINT == 4;            // input rows arrive in shared memory by cp.async.bulk
+    constexpr int PITCH = 512 * QX + 16;        // bytes per staged row: 16-byte halo slot + the CTA's pixels
     const int w = g.out_w, h = g.out_h;
     const int x0 = bx0 + lane * 4;
 
@@ -256,17 +284,29 @@ __device__ __forceinline__ void convert_tile(const SkGeom &g, const SkFrame &f, 
         }
     }
 
+    if (BULK && FULL) {
+        mbar_wait(bar, 0);
 #pragma unroll
-    for (int r = 0; r < ROWS; r++) {
-        const bool rv = FULL || (y0 + r) < h;
-        const uint8_t *row = in + (uint32_t)r * (uint32_t)g.in_stride;
+        for (int r = 0; r < ROWS; r++) {
+            const uint8_t *trow = tile + (warp * ROWS + r) * PITCH;
 #pragma unroll
-        for (int q = 0; q < QX; q++) {
-            if (FULL) px[r][q] = ld16<HINT>(row + q * 512);
-            else px[r][q] = load_quad<HINT>(row + q * 512, rv ? nvq[q] : 0);
+            for (int q = 0; q < QX; q++)
+                px[r][q] = *reinterpret_cast<const uint4 *>(trow + 16 + lane * 16 + q * 512);
+            halo[r] = want_halo ? *reinterpret_cast<const uint32_t *>(trow + 12) : 0u;
         }
-        halo[r] = 0;
-        if (want_halo && rv) halo[r] = ld4<0>(row - 4);   // lane 0: pixel left of the warp
+    } else {
+#pragma unroll
+        for (int r = 0; r < ROWS; r++) {
+            const bool rv = FULL || (y0 + r) < h;
+            const uint8_t *row = in + (uint32_t)r * (uint32_t)g.in_stride;
+#pragma unroll
+            for (int q = 0; q < QX; q++) {
+                if (FULL) px[r][q] = ld16<HINT>(row + q * 512);
+                else px[r][q] = load_quad<HINT>(row + q * 512, rv ? nvq[q] : 0);
+            }
+            halo[r] = 0;
+            if (want_halo && rv) halo[r] = ld4<0>(row - 4);   // lane 0: pixel left of the warp
+        }
     }
     // ---- phase 2: arithmetic, stores, compare
     uint8_t *oy = f.out + y_off;
@@ -365,7 +405,28 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
     }
     uint32_t diff[QX];
     int nvq[QX];
-    if (full) convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, true>(g, f, bx0, y0, lane, have_prev, diff, nvq);
+    constexpr bool BULK = HINT == 4;
+    constexpr int PITCH = 512 * QX + 16;
+    __shared__ __align__(16) uint8_t s_tile[BULK ? 16 * RP * PITCH : 16];
+    __shared__ __align__(8) unsigned long long s_bar;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+    if (BULK && full) {
+        // The TMA engine copies the CTA's 16*RP input rows (plus the 16-byte halo slot on the left)
+        // into shared memory; one lane per row issues, lane 0 arms the barrier with the byte total.
+        if (threadIdx.x == 0) mbar_init(bar, 1);
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t lead = bx0 > 0 ? 16u : 0u;
+            const uint32_t row_bytes = 512u * QX + lead;
+            if (lane == 0) mbar_expect_tx(bar, row_bytes * 16u * RP);
+            __syncwarp();
+            if (lane < 16 * RP) {
+                const uint8_t *src = f.in + (size_t)(by0 + lane) * (size_t)g.in_stride + 4 * (size_t)bx0 - lead;
+                bulk_g2s((uint32_t)__cvta_generic_to_shared(s_tile) + lane * PITCH + 16 - lead, src, row_bytes, bar);
+            }
+        }
+    }
+    if (full) convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, true>(g, f, bx0, y0, lane, have_prev, diff, nvq, s_tile, bar, warp);
     else      convert_tile<RP, QX, FMT, SITE, DAMAGE, HINT, false>(g, f, bx0, y0, lane, have_prev, diff, nvq);
 
     // ---- phase 3: per-macroblock flags
@@ -881,6 +942,7 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
     case 11: return launch_convert_shape<1, 4, 0>(g, b, n, st);
     case 12: return launch_convert_shape<1, 2, 2>(g, b, n, st);   // default shape, streaming stores
     case 13: return launch_convert_shape<1, 2, 3>(g, b, n, st);   // default shape, streaming loads + stores
+    case 14: return launch_convert_shape<1, 2, 4>(g, b, n, st);   // default shape, input rows staged by cp.async.bulk (TMA engine)
     }
 }
 
