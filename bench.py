@@ -349,9 +349,9 @@ def run_b200(args, rank, world, local_rank, dist):
         rr = esess[0].wait(esess[0].submit(k & 1))
         h2d.append(rr.h2d_us); d2h.append(rr.d2h_us)
     pcie = {"h2d_gbs_isolated": 4 * W * H / (statistics.median(h2d) * 1e-6) / 1e9,
-            "d2h_gbs_isolated": (frame_bytes + (2 * (W // 16) * (H // 16) + 4)) / (statistics.median(d2h) * 1e-6) / 1e9,
+            "d2h_gbs_isolated": (frame_bytes + 2 * (W // 16) * (H // 16)) / (statistics.median(d2h) * 1e-6) / 1e9,
             "how": "median of 8 single-frame submits, CUDA events around cudaMemcpyAsync from/to pinned memory"}
-    meta_bytes = 2 * (((r.damage_map.size + 3) // 4) * 4) + 4      # map + policy map + count
+    meta_bytes = 2 * (((r.damage_map.size + 3) // 4) * 4)      # damage map + policy map
     for s in esess:
         s.close()
 

@@ -33,6 +33,27 @@ thread_local std::string g_create_error;
 
 inline int ru(int v, int a) { return (v + a - 1) / a * a; }
 
+// Sum of n bytes that are each 0 or 1: eight at a time, folding before a lane can overflow.
+uint32_t sum_bytes(const uint8_t *p, size_t n)
+{
+    uint64_t total = 0;
+    size_t i = 0;
+    while (i + 8 <= n) {
+        uint64_t acc = 0;
+        const size_t stop = (n - i) / 8 < 255 ? i + (n - i) / 8 * 8 : i + 255 * 8;
+        for (; i < stop; i += 8) {
+            uint64_t v;
+            std::memcpy(&v, p + i, 8);
+            acc += v;
+        }
+        acc = (acc & 0x00ff00ff00ff00ffull) + ((acc >> 8) & 0x00ff00ff00ff00ffull);
+        acc = (acc & 0x0000ffff0000ffffull) + ((acc >> 16) & 0x0000ffff0000ffffull);
+        total += (acc & 0xffffffffull) + (acc >> 32);
+    }
+    for (; i < n; i++) total += p[i];
+    return (uint32_t)total;
+}
+
 struct Slot {          // one staging slot (caller-chosen index)
     uint8_t *h_in = nullptr;
     uint8_t *d_in = nullptr;
@@ -45,6 +66,8 @@ struct Ring {          // one output ring entry (submission order)
     uint8_t *h_out = nullptr;
     uint8_t *d_meta = nullptr;        // map bytes, policy bytes, then the u32 count
     uint8_t *h_meta = nullptr;
+    uint8_t *d_meta_view = nullptr;   // where this frame's maps actually are: own buffers, or a slice of
+    uint8_t *h_meta_view = nullptr;   // the batch leader's contiguous block (one D2H for the whole batch)
     cudaEvent_t h2d_start = nullptr, h2d_done = nullptr;
     cudaEvent_t k_start = nullptr, k_done = nullptr;
     cudaEvent_t d2h_start = nullptr, done = nullptr;
@@ -53,6 +76,8 @@ struct Ring {          // one output ring entry (submission order)
     bool valid = false;
     bool had_h2d = false;
     bool used = false;                // `done` has been recorded at least once
+    uint32_t count = 0;               // damaged blocks of this frame (host sum of the map)
+    bool count_valid = false;
 };
 
 }  // namespace
@@ -71,8 +96,9 @@ struct sk_session {
     int plane_stride[3]{};
     Slot slots[kMaxInflight];
     Ring ring[kMaxInflight];
-    uint32_t *d_scratch = nullptr;
     uint32_t *d_state = nullptr;      // per-macroblock temporal policy state
+    uint8_t *d_bmeta[kMaxInflight] = {};   // leader only: maps of all batch members, contiguous per ring entry
+    uint8_t *h_bmeta[kMaxInflight] = {};
     int32_t *d_voff = nullptr;
     int16_t *d_vtap = nullptr;
     cudaStream_t s_copy = nullptr, s_comp = nullptr, s_d2h = nullptr;
@@ -182,8 +208,11 @@ void free_session(sk_session *s)
         cudaEvent_t evs[] = {r.h2d_start, r.h2d_done, r.k_start, r.k_done, r.d2h_start, r.done};
         for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     }
-    if (s->d_scratch) cudaFree(s->d_scratch);
     if (s->d_state) cudaFree(s->d_state);
+    for (int i = 0; i < kMaxInflight; i++) {
+        if (s->d_bmeta[i]) cudaFree(s->d_bmeta[i]);
+        if (s->h_bmeta[i]) cudaFreeHost(s->h_bmeta[i]);
+    }
     if (s->d_voff) cudaFree(s->d_voff);
     if (s->d_vtap) cudaFree(s->d_vtap);
     for (cudaEvent_t e : s->mark) if (e) cudaEventDestroy(e);
@@ -237,15 +266,18 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.in = in;
     f.out = r.d_out;
     f.prev = (s->prev_ring >= 0) ? s->ring[s->prev_ring].d_out : nullptr;
+    r.d_meta_view = r.d_meta;
+    r.h_meta_view = r.h_meta;
     f.map = r.d_meta;
-    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta + 2 * s->map_bytes);
+    f.count_out = nullptr;                      // sessions count on the host (sk_wait)
     f.state = s->d_state;                       // nullptr unless SK_FLAG_POLICY
     f.policy = r.d_meta + s->map_bytes;
-    f.scratch = s->d_scratch;
+    f.scratch = nullptr;
     f.v_off = s->d_voff;
     f.v_tap = s->d_vtap;
     r.frame_id = frame_id;
     r.valid = true;
+    r.count_valid = false;
     s->prev_ring = ri;
     s->seq++;
     return ri;
@@ -270,7 +302,8 @@ int enqueue_readback(sk_session *s, int ri, cudaEvent_t kernel_done)
     SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, kernel_done, 0));
     if (timing) SK_CUDA(s, cudaEventRecord(r.d2h_start, s->s_d2h));
     if (damage)
-        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, s->meta_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
+        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, s->d_state ? s->meta_bytes : s->map_bytes,
+                                   cudaMemcpyDeviceToHost, s->s_d2h));
     if (host_out)
         SK_CUDA(s, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
     SK_CUDA(s, cudaEventRecord(r.done, s->s_d2h));
@@ -431,7 +464,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     g.in_stride = s->d_in_stride;
     s->in_bytes_host = (size_t)c.in_stride * c.in_height;
     s->map_bytes = (size_t)ru(g.mb_w * g.mb_h, 4);
-    s->meta_bytes = 2 * s->map_bytes + 4;
+    s->meta_bytes = 2 * s->map_bytes;
 
     SK_TRY(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
     SK_TRY(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
@@ -454,8 +487,6 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         cudaEvent_t *evs[] = {&r.h2d_start, &r.h2d_done, &r.k_start, &r.k_done, &r.d2h_start, &r.done};
         for (cudaEvent_t *ev : evs) SK_TRY(cudaEventCreateWithFlags(ev, evflags));
     }
-    SK_TRY(cudaMalloc((void **)&s->d_scratch, 256));
-    SK_TRY(cudaMemset(s->d_scratch, 0, 256));
     if ((c.flags & SK_FLAG_POLICY) && !(c.flags & SK_FLAG_NO_DAMAGE)) {
         SK_TRY(cudaMalloc((void **)&s->d_state, s->map_bytes * sizeof(uint32_t)));
         SK_TRY(cudaMemset(s->d_state, 0, s->map_bytes * sizeof(uint32_t)));
@@ -676,17 +707,35 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
         ris[i] = stage_frame(s, (const uint8_t *)dptrs[i], frame_id, b.f[i]);
     }
     Ring &lr = L->ring[ris[0]];
+    const bool damage = !(L->cfg.flags & SK_FLAG_NO_DAMAGE);
+    if (damage) {
+        // All members' maps land in one block owned by the leader (allocated at the first batch), so the
+        // read-back is ONE copy per step instead of one small copy per session.
+        const int lri = ris[0];
+        if (!L->d_bmeta[lri]) {
+            SK_CUDA(L, cudaMalloc((void **)&L->d_bmeta[lri], (size_t)SK_MAX_BATCH * L->meta_bytes));
+            SK_CUDA(L, cudaHostAlloc((void **)&L->h_bmeta[lri], (size_t)SK_MAX_BATCH * L->meta_bytes, cudaHostAllocDefault));
+        }
+        for (int i = 0; i < n; i++) {
+            Ring &r = ss[i]->ring[ris[i]];
+            r.d_meta_view = L->d_bmeta[lri] + (size_t)i * L->meta_bytes;
+            r.h_meta_view = L->h_bmeta[lri] + (size_t)i * L->meta_bytes;
+            b.f[i].map = r.d_meta_view;
+            b.f[i].policy = r.d_meta_view + L->map_bytes;
+        }
+    }
     if (timing) SK_CUDA(L, cudaEventRecord(lr.k_start, L->s_comp));
     SK_CUDA(L, launch(L, g, b, n, L->s_comp));
     SK_CUDA(L, cudaEventRecord(lr.k_done, L->s_comp));
     // Read-back of every member rides on the leader's d2h stream; one event closes the batch.
     SK_CUDA(L, cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
     if (timing) SK_CUDA(L, cudaEventRecord(lr.d2h_start, L->s_d2h));
+    if (damage)
+        SK_CUDA(L, cudaMemcpyAsync(L->h_bmeta[ris[0]], L->d_bmeta[ris[0]], (size_t)n * L->meta_bytes,
+                                   cudaMemcpyDeviceToHost, L->s_d2h));
     for (int i = 0; i < n; i++) {
         sk_session *s = ss[i];
         Ring &r = s->ring[ris[i]];
-        if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE))
-            SK_CUDA(L, cudaMemcpyAsync(r.h_meta, r.d_meta, s->meta_bytes, cudaMemcpyDeviceToHost, L->s_d2h));
         if (s->cfg.flags & SK_FLAG_HOST_OUTPUT)
             SK_CUDA(L, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, L->s_d2h));
     }
@@ -730,14 +779,16 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
         out->mb_w = s->geom.mb_w;
         out->mb_h = s->geom.mb_h;
         if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) {
-            out->host_damage_map = r.h_meta;
-            out->dev_damage_map = r.d_meta;
-            uint32_t cnt;
-            std::memcpy(&cnt, r.h_meta + 2 * s->map_bytes, 4);
-            out->damaged_count = cnt;
+            out->host_damage_map = r.h_meta_view;
+            out->dev_damage_map = r.d_meta_view;
+            if (!r.count_valid) {                 // exact sum of the 0/1 map bytes, once per frame
+                r.count = sum_bytes(r.h_meta_view, (size_t)s->geom.mb_w * s->geom.mb_h);
+                r.count_valid = true;
+            }
+            out->damaged_count = r.count;
             if (s->d_state) {
-                out->host_policy_map = r.h_meta + s->map_bytes;
-                out->dev_policy_map = r.d_meta + s->map_bytes;
+                out->host_policy_map = r.h_meta_view + s->map_bytes;
+                out->dev_policy_map = r.d_meta_view + s->map_bytes;
             }
         }
         if (timing && own_events) {
@@ -756,13 +807,35 @@ int sk_batch_wait(sk_session **ss, int n, uint64_t frame_id, uint32_t *damaged_c
     if (!ss || n < 1 || !ss[0]) return SK_ERR_ARG;
     for (int i = 0; i < n; i++) {
         if (!ss[i]) return fail(ss[0], SK_ERR_ARG, "null session in batch");
-        sk_result r;
-        int rc = sk_wait(ss[i], frame_id, &r);
-        if (rc != SK_OK) {
-            if (i > 0) ss[0]->err = ss[i]->err;
-            return rc;
+        if (i == 0 || !damaged_counts) {
+            sk_result r;
+            int rc = sk_wait(ss[i], frame_id, &r);
+            if (rc != SK_OK) {
+                if (i > 0) ss[0]->err = ss[i]->err;
+                return rc;
+            }
+            if (damaged_counts) damaged_counts[i] = r.damaged_count;
+            continue;
         }
-        if (damaged_counts) damaged_counts[i] = r.damaged_count;
+        // members of one batch share the leader's completion event: after the leader's wait only the
+        // host-side sum is left (a member submitted outside the batch falls back to a full sk_wait)
+        sk_session *s = ss[i];
+        const int ri = find_ring(s, frame_id);
+        if (ri < 0) return fail(ss[0], SK_ERR_STATE, "unknown frame id in batch");
+        Ring &r = s->ring[ri];
+        const int lri = find_ring(ss[0], frame_id);
+        if (lri < 0 || r.wait_on != ss[0]->ring[lri].wait_on || (s->cfg.flags & SK_FLAG_NO_DAMAGE)) {
+            sk_result res;
+            int rc = sk_wait(s, frame_id, &res);
+            if (rc != SK_OK) { ss[0]->err = s->err; return rc; }
+            damaged_counts[i] = res.damaged_count;
+            continue;
+        }
+        if (!r.count_valid) {
+            r.count = sum_bytes(r.h_meta_view, (size_t)s->geom.mb_w * s->geom.mb_h);
+            r.count_valid = true;
+        }
+        damaged_counts[i] = r.count;
     }
     return SK_OK;
 }

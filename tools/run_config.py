@@ -11,6 +11,9 @@ from selkies_gstreamer_b200 import synth  # noqa: E402
 
 w, h, ow, oh = (int(x) for x in sys.argv[1:5])
 fmt, batch, steps = sys.argv[5], int(sys.argv[6]), int(sys.argv[7])
+if len(sys.argv) > 8:
+    from selkies_gstreamer_b200 import _abi
+    _abi.load().sk_set_kernel_variant(int(sys.argv[8]))
 sess = [sk.PreencodeSession(w, h, out_width=ow, out_height=oh, out_format=fmt, colorimetry="bt709",
                             chroma_site="mpeg2", host_output=False, timing=(i == 0)) for i in range(batch)]
 base = synth.desktop(w, h)
@@ -24,4 +27,10 @@ stride = sess[0].device_input(0)[1]
 for k in range(steps):
     b.submit(sets[k & 1], stride, 100 + k)
     b.wait(100 + k)
-print("kernel_us", sess[0].last_kernel_us())
+import statistics
+ks = []
+for k in range(steps, steps + 30):
+    b.submit(sets[k & 1], stride, 100 + k)
+    b.wait(100 + k)
+    ks.append(sess[0].last_kernel_us())
+print("kernel_us", round(statistics.median(ks), 2))
