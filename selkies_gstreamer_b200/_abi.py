@@ -82,7 +82,7 @@ class PreencodeLibraryError(RuntimeError):
 
 def build(force: bool = False) -> str:
     """Compile the library in-tree with nvcc for sm_100a (seconds; works without a GPU)."""
-    srcs = [os.path.join(CSRC, f) for f in ("sk_kernels.cu", "sk_session.cu", "sk_noalloc.cu", "sk_kernels.h")]
+    srcs = [os.path.join(CSRC, f) for f in ("sk_kernels.cu", "sk_session.cu", "sk_noalloc.cu", "sk_kernels.h", "sk_host_math.h")]
     srcs.append(os.path.join(_PKG, "..", "include", "selkies_preencode.h"))
     stale = (not os.path.exists(LIB_PATH)
              or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(s) for s in srcs))

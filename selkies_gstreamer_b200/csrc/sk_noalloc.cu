@@ -22,6 +22,7 @@
 // GPU that loads the library carries that array (about 26 KB) until the process exits.
 #include "../../include/selkies_preencode.h"
 #include "sk_kernels.h"
+#include "sk_host_math.h"
 
 #include <cmath>
 #include <cstdarg>
@@ -60,60 +61,6 @@ int fail(char *errbuf, size_t n, int code, const char *fmt, ...)
         va_end(ap);
     }
     return code;
-}
-
-inline int ru(int v, int a) { return (v + a - 1) / a * a; }
-
-// Same integer matrix as the session path: full-range RGB → limited-range Y'CbCr at
-// 8 fractional bits, each entry rounded to nearest-even.
-void coeffs(int matrix, int c[3][3])
-{
-    double kr = 0.299, kb = 0.114;
-    if (matrix == SK_MATRIX_BT709) { kr = 0.2126; kb = 0.0722; }
-    else if (matrix == SK_MATRIX_BT2020) { kr = 0.2627; kb = 0.0593; }
-    const double kg = 1.0 - kr - kb, inv255 = 1 / ((float)255);
-    const double ys = 219.0 * inv255 * 256.0, cs = 224.0 * inv255 * 256.0;
-    const double ub = 1 / (2 * (1 - kb)), vr = 1 / (2 * (1 - kr));
-    const double m[3][3] = {{kr * ys, kg * ys, kb * ys},
-                            {-ub * kr * cs, -ub * kg * cs, ub * (1 - kb) * cs},
-                            {vr * (1 - kr) * cs, -vr * kg * cs, -vr * kb * cs}};
-    for (int i = 0; i < 3; i++)
-        for (int j = 0; j < 3; j++) c[i][j] = (int)std::nearbyint(m[i][j]);
-}
-
-uint32_t pack(const int c[3], int in_fmt)
-{
-    uint32_t r = (uint32_t)(c[0] & 0xff), g = (uint32_t)(c[1] & 0xff), b = (uint32_t)(c[2] & 0xff);
-    return in_fmt == SK_IN_BGRX ? (b | (g << 8) | (r << 16)) : (r | (g << 8) | (b << 16));
-}
-
-// 2-tap vertical table of the linear resampler, as in the session path.
-void vertical_taps(int in_size, int out_size, int variant, int32_t *off, int16_t *tap)
-{
-    const double ratio = (double)in_size / out_size;
-    const double stretch = (variant == SK_SCALE_VARIANT_GST_LQ && ratio > 1.0) ? 1.0 / ratio : 1.0;
-    for (int j = 0; j < out_size; j++) {
-        double pos = (j + 0.5) / out_size * in_size - 0.5;
-        pos = std::fmin(std::fmax(pos, 0.0), (double)(in_size - 1));
-        int first = (int)std::floor(pos);
-        double w[2];
-        for (int l = 0; l < 2; l++) {
-            double a = std::fabs(pos - (first + l)) * stretch;
-            w[l] = a < 1.0 ? 1.0 - a : 0.0;
-        }
-        const double sum = w[0] + w[1];
-        w[0] /= sum;  w[1] /= sum;
-        if (first > in_size - 2) { w[1] += w[0]; w[0] = 0.0; first = in_size - 2; }
-        double lo = 0.0, hi = 1.0, bias = 0.5;
-        for (int it = 0; it < 64; it++) {
-            int s = (int)std::floor(bias + w[0] * 64.0) + (int)std::floor(bias + w[1] * 64.0);
-            if (s == 64 || lo == hi) break;
-            if (s < 64) { if (bias > lo) lo = bias; bias += (hi - lo) / 2; }
-            else        { if (bias < hi) hi = bias; bias -= (hi - lo) / 2; }
-        }
-        off[j] = first;
-        tap[j] = (int16_t)std::floor(bias + w[1] * 64.0);
-    }
 }
 
 }  // namespace
@@ -180,40 +127,16 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
     if ((e = cudaMemsetAsync(d_counters, 0, kCounterBytes, st)) != cudaSuccess)
         return fail(errbuf, errbuf_len, SK_ERR_CUDA, "cudaMemsetAsync(scratch counters): %s", cudaGetErrorString(e));
     if (in_h != out_h) {
-        vertical_taps(in_h, out_h, cfg->scale_variant, g_host_off, g_host_tap);
+        skhost::vertical_taps(in_h, out_h, cfg->scale_variant, g_host_off, g_host_tap);
         if ((e = cudaMemcpyAsync(d_off, g_host_off, sizeof(int32_t) * out_h, cudaMemcpyHostToDevice, st)) != cudaSuccess ||
             (e = cudaMemcpyAsync(d_tap, g_host_tap, sizeof(int16_t) * out_h, cudaMemcpyHostToDevice, st)) != cudaSuccess)
             return fail(errbuf, errbuf_len, SK_ERR_CUDA, "cudaMemcpyAsync(tap tables): %s", cudaGetErrorString(e));
     }
 
     SkGeom g{};
-    g.in_w = in_w;  g.in_h = in_h;  g.out_w = out_w;  g.out_h = out_h;
+    skhost::fill_geometry(g, in_w, in_h, out_w, out_h, cfg->in_format, cfg->out_format, cfg->matrix,
+                          cfg->chroma_site, damage);
     g.in_stride = (int)in_stride;
-    const int h2 = ru(out_h, 2);
-    g.y_stride = ru(out_w, 4);
-    if (cfg->out_format == SK_OUT_I420) {
-        g.c_stride = ru(ru(out_w, 2) / 2, 4);
-        g.off_c0 = (uint32_t)g.y_stride * h2;
-        g.off_c1 = g.off_c0 + (uint32_t)g.c_stride * (h2 / 2);
-    } else {
-        g.c_stride = g.y_stride;
-        g.off_c0 = (uint32_t)g.y_stride * h2;
-        g.off_c1 = 0;
-    }
-    g.mb_w = (out_w + 15) / 16;
-    g.mb_h = (out_h + 15) / 16;
-    int m[3][3];
-    coeffs(cfg->matrix, m);
-    g.cy = pack(m[0], cfg->in_format);
-    g.cu = pack(m[1], cfg->in_format);
-    g.cv = pack(m[2], cfg->in_format);
-    g.out_fmt = cfg->out_format;
-    g.site = cfg->chroma_site;
-    g.damage = damage ? 1 : 0;
-    g.scale_h = in_w != out_w;
-    g.scale_v = in_h != out_h;
-    g.h_inc = out_w > 1 ? (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - 1) : 0;
-    g.h_first = ((int64_t)out_w * in_h <= (int64_t)in_w * out_h) ? 1 : 0;
 
     SkBatch b{};
     b.f[0].in = static_cast<const uint8_t *>(d_in);

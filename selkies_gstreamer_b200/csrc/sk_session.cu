@@ -12,6 +12,7 @@
 //   d2h stream    : map+count (and the frame with SK_FLAG_HOST_OUTPUT) to pinned host
 #include "../../include/selkies_preencode.h"
 #include "sk_kernels.h"
+#include "sk_host_math.h"
 
 #include <atomic>
 #include <cmath>
@@ -31,7 +32,7 @@ std::atomic<int> g_snake{1};            // alternate traversal direction per lau
 std::atomic<int> g_scale_generic{0};   // tuning/testing: force the generic scale kernel
 thread_local std::string g_create_error;
 
-inline int ru(int v, int a) { return (v + a - 1) / a * a; }
+using skhost::ru;
 
 // Sum of n bytes that are each 0 or 1: eight at a time, folding before a lane can overflow.
 uint32_t sum_bytes(const uint8_t *p, size_t n)
@@ -125,68 +126,6 @@ int fail(sk_session *s, int code, const std::string &msg)
         if (e_ != cudaSuccess)                                                               \
             return fail((s), SK_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
-
-// Integer colour matrix at 8 fractional bits: full-range RGB → limited-range
-// Y'CbCr, each entry rounded to nearest-even.
-void matrix_coeffs(int matrix, int c[3][3])
-{
-    double kr = 0.299, kb = 0.114;
-    if (matrix == SK_MATRIX_BT709) { kr = 0.2126; kb = 0.0722; }
-    else if (matrix == SK_MATRIX_BT2020) { kr = 0.2627; kb = 0.0593; }
-    const double kg = 1.0 - kr - kb;
-    const double inv255 = 1 / ((float)255);
-    const double ys = 219.0 * inv255 * 256.0, cs = 224.0 * inv255 * 256.0;
-    const double ub = 1 / (2 * (1 - kb)), vr = 1 / (2 * (1 - kr));
-    const double m[3][3] = {
-        {kr * ys, kg * ys, kb * ys},
-        {-ub * kr * cs, -ub * kg * cs, ub * (1 - kb) * cs},
-        {vr * (1 - kr) * cs, -vr * kg * cs, -vr * kb * cs}};
-    for (int i = 0; i < 3; i++)
-        for (int j = 0; j < 3; j++)
-            c[i][j] = (int)std::nearbyint(m[i][j]);
-}
-
-uint32_t pack_coeffs(const int c[3], int in_fmt)
-{
-    // c = {R, G, B}; byte k of the result multiplies byte k of the pixel word.
-    uint32_t r = (uint32_t)(c[0] & 0xff), g = (uint32_t)(c[1] & 0xff), b = (uint32_t)(c[2] & 0xff);
-    if (in_fmt == SK_IN_BGRX) return b | (g << 8) | (r << 16);
-    return r | (g << 8) | (b << 16);
-}
-
-// 2-tap vertical table of the linear resampler (videoscale method=bilinear):
-// centre-aligned source position, triangle filter (stretched by out/in when
-// shrinking in the GST_LQ variant), two taps renormalised, 6-bit integer taps
-// found by a bias search so that they sum to 64.
-void vertical_taps(int in_size, int out_size, int variant, std::vector<int32_t> &off, std::vector<int16_t> &tap)
-{
-    off.resize(out_size);
-    tap.resize(out_size);
-    const double ratio = (double)in_size / out_size;
-    const double stretch = (variant == SK_SCALE_VARIANT_GST_LQ && ratio > 1.0) ? 1.0 / ratio : 1.0;
-    for (int j = 0; j < out_size; j++) {
-        double pos = (j + 0.5) / out_size * in_size - 0.5;
-        pos = std::fmin(std::fmax(pos, 0.0), (double)(in_size - 1));
-        int first = (int)std::floor(pos);
-        double w[2];
-        for (int l = 0; l < 2; l++) {
-            double a = std::fabs(pos - (first + l)) * stretch;
-            w[l] = a < 1.0 ? 1.0 - a : 0.0;
-        }
-        const double sum = w[0] + w[1];
-        w[0] /= sum;  w[1] /= sum;
-        if (first > in_size - 2) { w[1] += w[0]; w[0] = 0.0; first = in_size - 2; }
-        double lo = 0.0, hi = 1.0, bias = 0.5;
-        for (int it = 0; it < 64; it++) {
-            int s = (int)std::floor(bias + w[0] * 64.0) + (int)std::floor(bias + w[1] * 64.0);
-            if (s == 64 || lo == hi) break;
-            if (s < 64) { if (bias > lo) lo = bias; bias += (hi - lo) / 2; }
-            else        { if (bias < hi) hi = bias; bias -= (hi - lo) / 2; }
-        }
-        off[j] = first;
-        tap[j] = (int16_t)std::floor(bias + w[1] * 64.0);
-    }
-}
 
 void free_session(sk_session *s)
 {
@@ -424,42 +363,14 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     SK_TRY(cudaSetDevice(s->dev));
     // geometry (GstVideoInfo default layout)
     SkGeom &g = s->geom;
-    g.in_w = c.in_width;  g.in_h = c.in_height;
-    g.out_w = c.out_width;  g.out_h = c.out_height;
-    const int h2 = ru(g.out_h, 2);
-    g.y_stride = ru(g.out_w, 4);
-    if (c.out_format == SK_OUT_I420) {
-        g.c_stride = ru(ru(g.out_w, 2) / 2, 4);
-        g.off_c0 = (uint32_t)g.y_stride * h2;
-        g.off_c1 = g.off_c0 + (uint32_t)g.c_stride * (h2 / 2);
-        s->frame_bytes = (size_t)g.off_c1 + (size_t)g.c_stride * (h2 / 2);
-        s->plane_offset[0] = 0; s->plane_offset[1] = g.off_c0; s->plane_offset[2] = g.off_c1;
-        s->plane_stride[0] = g.y_stride; s->plane_stride[1] = g.c_stride; s->plane_stride[2] = g.c_stride;
-    } else {
-        g.c_stride = g.y_stride;
-        g.off_c0 = (uint32_t)g.y_stride * h2;
-        g.off_c1 = 0;
-        s->frame_bytes = (size_t)g.off_c0 + (size_t)g.c_stride * (h2 / 2);
-        s->plane_offset[0] = 0; s->plane_offset[1] = g.off_c0; s->plane_offset[2] = 0;
-        s->plane_stride[0] = g.y_stride; s->plane_stride[1] = g.c_stride; s->plane_stride[2] = 0;
-    }
-    g.mb_w = (g.out_w + 15) / 16;
-    g.mb_h = (g.out_h + 15) / 16;
-    int m[3][3];
-    matrix_coeffs(c.matrix, m);
-    g.cy = pack_coeffs(m[0], c.in_format);
-    g.cu = pack_coeffs(m[1], c.in_format);
-    g.cv = pack_coeffs(m[2], c.in_format);
-    g.out_fmt = c.out_format;
-    g.site = c.chroma_site;
-    g.damage = (c.flags & SK_FLAG_NO_DAMAGE) ? 0 : 1;
+    s->frame_bytes = skhost::fill_geometry(g, c.in_width, c.in_height, c.out_width, c.out_height, c.in_format,
+                                           c.out_format, c.matrix, c.chroma_site, !(c.flags & SK_FLAG_NO_DAMAGE));
+    s->plane_offset[0] = 0;  s->plane_offset[1] = g.off_c0;  s->plane_offset[2] = g.off_c1;
+    s->plane_stride[0] = g.y_stride;  s->plane_stride[1] = g.c_stride;
+    s->plane_stride[2] = (c.out_format == SK_OUT_I420) ? g.c_stride : 0;
     g.pol_threshold = c.damage_block_threshold;
     g.pol_duration = c.damage_block_duration;
     g.pol_trigger = c.paint_over_trigger_frames;
-    g.scale_h = g.in_w != g.out_w;
-    g.scale_v = g.in_h != g.out_h;
-    g.h_inc = g.out_w > 1 ? (int32_t)((((int64_t)g.in_w - 1) << 16) / (g.out_w - 1) - 1) : 0;
-    g.h_first = ((int64_t)g.out_w * g.in_h <= (int64_t)g.in_w * g.out_h) ? 1 : 0;
     s->d_in_stride = ru(c.in_stride, 16);
     g.in_stride = s->d_in_stride;
     s->in_bytes_host = (size_t)c.in_stride * c.in_height;
@@ -495,7 +406,9 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     if (s->scaling) {
         std::vector<int32_t> off;
         std::vector<int16_t> tap;
-        vertical_taps(g.in_h, g.out_h, c.scale_variant, off, tap);
+        off.resize(g.out_h);
+        tap.resize(g.out_h);
+        skhost::vertical_taps(g.in_h, g.out_h, c.scale_variant, off.data(), tap.data());
         // The tiled kernel needs the h pass first (or a single axis) and every 16-row output
         // tile's source rows inside its shared-memory window (36 rows).
         int max_rows = 16;
