@@ -32,7 +32,7 @@ def regions_from_mask(mask: np.ndarray, width: int, height: int, kind: str = "da
                       max_regions: int = 64) -> list[Region]:
     """Cover the set macroblocks with rectangles: horizontal runs per macroblock row, runs with
     the same span in consecutive rows merged vertically.  If more than max_regions result, fall
-    back to one bounding rectangle per macroblock row band, then to one bounding box."""
+    back to one bounding rectangle per band of macroblock rows (at most max_regions bands)."""
     mask = np.asarray(mask).astype(bool)
     mbh, mbw = mask.shape
     open_runs: dict[tuple[int, int], list[int]] = {}      # (x0, x1) -> [y0, y1)
@@ -56,8 +56,14 @@ def regions_from_mask(mask: np.ndarray, width: int, height: int, kind: str = "da
     for (x0, x1), (y0, y1) in open_runs.items():
         done.append((x0, y0, x1, y1))
     if len(done) > max_regions:
-        ys, xs = np.nonzero(mask)
-        done = [(int(xs.min()), int(ys.min()), int(xs.max()) + 1, int(ys.max()) + 1)]
+        # too fragmented for per-run rectangles: one bounding box per band of macroblock rows
+        band = -(-mbh // max_regions)
+        done = []
+        for y0 in range(0, mbh, band):
+            sub = mask[y0:y0 + band]
+            if sub.any():
+                ys, xs = np.nonzero(sub)
+                done.append((int(xs.min()), y0 + int(ys.min()), int(xs.max()) + 1, y0 + int(ys.max()) + 1))
     out = []
     for (x0, y0, x1, y1) in sorted(done, key=lambda r: (r[1], r[0])):
         px, py = x0 * MB, y0 * MB

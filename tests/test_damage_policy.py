@@ -117,11 +117,18 @@ def test_equal_runs_in_consecutive_rows_merge_vertically():
     assert regions_from_mask(mask, 192, 160) == [Region(48, 32, 80, 64), Region(0, 112, 32, 16)]
 
 
-def test_too_many_regions_fall_back_to_bounding_box():
+def test_too_many_regions_fall_back_to_row_band_boxes():
     mask = np.zeros((20, 30), bool)
     mask[2:18:2, 3:27:2] = True
     regs = regions_from_mask(mask, 480, 320, max_regions=16)
-    assert regs == [Region(48, 32, 368, 240)]
+    assert 1 <= len(regs) <= 16
+    img = paint(regs, 30, 20, 480, 320)
+    assert img.max() == 1                                         # bands do not overlap
+    want = np.kron(mask.astype(np.int32), np.ones((16, 16), np.int32))
+    assert (img[want == 1] == 1).all()                            # every damaged block is covered
+    assert all(r.x == 48 and r.w == 23 * 16 for r in regs)        # each band's box spans columns 3..25
+    one = regions_from_mask(mask, 480, 320, max_regions=1)
+    assert one == [Region(48, 32, 368, 240)]
 
 
 def test_decisions():
