@@ -467,20 +467,32 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
 // 2-tap shrink in the RGB domain before the matrix (order as upstream's
 // chain_scale: h first when out_w*in_h <= in_w*out_h), then the same
 // matrix/chroma/damage tail.  Thread = 4 output pixels x 2 rows.
-__device__ __forceinline__ uint32_t lerp_h(uint32_t a, uint32_t b, uint32_t f)
+// 2-tap blends on the dot-product unit: the two pixels' bytes are interleaved per channel
+// ([aB bB aG bG], [aR bR . .]) and dp2a multiplies each byte pair by the 16-bit weight pair.
+// Both weight pairs sum to 256, so every result is byte 1 of its accumulator (X is dropped: the
+// matrix ignores it).
+__device__ __forceinline__ uint32_t blend2(uint32_t a, uint32_t b, uint32_t wpair, uint32_t round)
 {
-    // per byte: (a*(256-f) + b*f) >> 8, two 16-bit lanes at a time
-    uint32_t e = ((a & 0x00ff00ffu) * (256u - f) + (b & 0x00ff00ffu) * f) >> 8;
-    uint32_t o = (((a >> 8) & 0x00ff00ffu) * (256u - f) + ((b >> 8) & 0x00ff00ffu) * f) >> 8;
-    return (e & 0x00ff00ffu) | ((o & 0x00ff00ffu) << 8);
+    const uint32_t t0 = __byte_perm(a, b, 0x5140);     // aB bB aG bG
+    const uint32_t t1 = __byte_perm(a, b, 0x7362);     // aR bR aX bX
+    const uint32_t rb = __dp2a_lo(wpair, t0, round);
+    const uint32_t rg = __dp2a_hi(wpair, t0, round);
+    const uint32_t rr = __dp2a_lo(wpair, t1, round);
+    return __byte_perm(__byte_perm(rb, rg, 0x0051), rr, 0x7510);
 }
-__device__ __forceinline__ uint32_t lerp_v(uint32_t a, uint32_t b, uint32_t p)
+// per byte (a*(256-f) + b*f) >> 8
+__device__ __forceinline__ uint32_t lerp_h2(uint32_t a, uint32_t b, uint32_t f)
 {
-    // per byte: a + (((b-a)*p + 32) >> 6)  ==  (a*(64-p) + b*p + 32) >> 6   (0 <= p <= 64)
-    uint32_t e = ((a & 0x00ff00ffu) * (64u - p) + (b & 0x00ff00ffu) * p + 0x00200020u) >> 6;
-    uint32_t o = (((a >> 8) & 0x00ff00ffu) * (64u - p) + ((b >> 8) & 0x00ff00ffu) * p + 0x00200020u) >> 6;
-    return (e & 0x00ff00ffu) | ((o & 0x00ff00ffu) << 8);
+    return blend2(a, b, (256u - f) | (f << 16), 0u);
 }
+// per byte (a*(64-p) + b*p + 32) >> 6  ==  (a*(256-4p) + b*4p + 128) >> 8   (0 <= p <= 64)
+__device__ __forceinline__ uint32_t lerp_v2(uint32_t a, uint32_t b, uint32_t p)
+{
+    return blend2(a, b, (256u - 4u * p) | ((4u * p) << 16), 128u);
+}
+
+__device__ __forceinline__ uint32_t lerp_h(uint32_t a, uint32_t b, uint32_t f) { return lerp_h2(a, b, f); }
+__device__ __forceinline__ uint32_t lerp_v(uint32_t a, uint32_t b, uint32_t p) { return lerp_v2(a, b, p); }
 
 __device__ __forceinline__ uint32_t sample_px(const uint8_t *in, const SkGeom &g, int x, int o, int o2, uint32_t p)
 {
@@ -626,21 +638,6 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
 //   B  each thread takes 4 adjacent output pixels x 2 rows with 128-bit LDS, applies the
 //      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
 constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
-
-__device__ __forceinline__ uint32_t lerp_h2(uint32_t a, uint32_t b, uint32_t f)
-{
-    const uint32_t w1 = f, w0 = 256u - f;
-    uint32_t e = (a & 0x00ff00ffu) * w0 + (b & 0x00ff00ffu) * w1;
-    uint32_t o = __byte_perm(a, 0, 0x4341) * w0 + __byte_perm(b, 0, 0x4341) * w1;
-    return __byte_perm(e, o, 0x7351);           // byte 1 of every 16-bit lane = (..)>>8
-}
-__device__ __forceinline__ uint32_t lerp_v2(uint32_t a, uint32_t b, uint32_t p)
-{
-    const uint32_t w1 = p, w0 = 64u - p;
-    uint32_t e = (a & 0x00ff00ffu) * w0 + ((b & 0x00ff00ffu) * w1 + 0x00200020u);
-    uint32_t o = __byte_perm(a, 0, 0x4341) * w0 + (__byte_perm(b, 0, 0x4341) * w1 + 0x00200020u);
-    return ((e >> 6) & 0x00ff00ffu) | ((o << 2) & 0xff00ff00u);
-}
 
 __device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g)
 {
