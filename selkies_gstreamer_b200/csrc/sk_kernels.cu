@@ -655,7 +655,8 @@ __device__ __forceinline__ void cp_async_commit_wait()
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
                                            const int bx0, const int by0, const int lane, const int warp,
-                                           const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out)
+                                           const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out,
+                                           const uint32_t bar)
 {
     const int w = g.out_w, h = g.out_h;
 
@@ -713,7 +714,21 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     const int cx0 = xs_first & ~3;                                    // 16-byte aligned start
     const int nch = ((xs_last - cx0) >> 2) + 1;                       // <= 96 (host-checked)
     const uint32_t RSB = 4u * (uint32_t)g.scale_raw_stride;           // bytes per raw row
-    {
+    // Rows whose last chunk would run past the end of the source row (in_w even but not a multiple of
+    // 4, right edge only) keep the per-chunk cp.async path; every other tile lets the TMA engine copy
+    // each window row with ONE cp.async.bulk issued by one lane, completion on an mbarrier.
+    const bool bulk = cx0 + 4 * nch <= g.in_w;            // CTA-uniform
+    if (bulk) {
+        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0;
+        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW);
+        const uint32_t row_bytes = 16u * (uint32_t)nch;
+        if (warp == 0 && lane == 0) mbar_expect_tx(bar, row_bytes * (uint32_t)nr);
+        if (lane < RPW) {                                  // lane i of warp w copies window row w + 8*i
+            const int r = warp + 8 * lane;
+            if (r < nr) bulk_g2s(raw_s + (uint32_t)r * RSB, base + (size_t)r * (size_t)g.in_stride, row_bytes, bar);
+        }
+        mbar_wait(bar, 0);
+    } else {
         const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0 + 16 * lane;
         const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + 16u * (uint32_t)lane;
         const int rem_px = g.in_w - cx0 - 4 * lane;      // pixels from this lane's first chunk to the row end
@@ -733,8 +748,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             }
         }
         cp_async_commit_wait();
+        __syncthreads();
     }
-    __syncthreads();
 
     // ---- pass A: h-scale (or copy) the window once into the second shared buffer; lanes own
     //      adjacent output columns, so the gathers are (nearly) bank-conflict free
@@ -866,12 +881,16 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 <= g.out_w) && (by0 + 16 <= g.out_h);
 
+    __shared__ __align__(8) unsigned long long s_bar;
+    const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+    if (threadIdx.x == 0) mbar_init(bar, 1);
+    __syncthreads();
     const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8, blockIdx.x * 8 + threadIdx.x, blockIdx.y) : 0u;
     uint32_t diff = 0;
     int nvx = 0;
     bool rows_valid = false;
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[8];
