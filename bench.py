@@ -96,6 +96,8 @@ class ClockSampler:
         sm, mx, reasons, inside = [], [], set(), 0
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
+            if t_begin is not None and r[0] < t_begin:
+                continue                       # before the timed region (warm-up)
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
             except (ValueError, IndexError):
@@ -237,13 +239,13 @@ def run_b200(args, rank, world, local_rank, dist):
         nonlocal counts
         counts = batch.wait(fid - 1)
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()                            # nvidia-smi needs a moment to come up (longer on an 8-GPU box)
     for k in range(args.warmup):
         step(k)
     sync_all()
     if dist:
         dist.barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     launches0 = sk.launch_count()
     kernel_us = []
     leader.marker(0)
@@ -260,7 +262,11 @@ def run_b200(args, rank, world, local_rank, dist):
     launches = sk.launch_count() - launches0
     t_end = time.perf_counter()
     k = args.steps + args.warmup
-    while time.perf_counter() - t0 < 0.4:      # nvidia-smi samples every 50 ms: keep the same load up, untimed
+    def samples_under_load():
+        return sum(1 for r in sampler.rows if r[0] >= t0)
+
+    # nvidia-smi samples every 50 ms: keep the same load up, untimed, until a few samples exist
+    while (time.perf_counter() - t0 < 0.4 or samples_under_load() < 3) and time.perf_counter() - t0 < 5.0:
         step(k)
         k += 1
     sync_all()
