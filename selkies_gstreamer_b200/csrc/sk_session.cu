@@ -595,7 +595,7 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
             a.out_format != b.out_format || a.matrix != b.matrix || a.chroma_site != b.chroma_site ||
             a.scale_variant != b.scale_variant || ((a.flags ^ b.flags) & (SK_FLAG_NO_DAMAGE | SK_FLAG_POLICY)) ||
             a.damage_block_threshold != b.damage_block_threshold || a.damage_block_duration != b.damage_block_duration ||
-            a.paint_over_trigger_frames != b.paint_over_trigger_frames)
+            a.paint_over_trigger_frames != b.paint_over_trigger_frames || a.n_inflight != b.n_inflight)
             return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
         for (int j = 0; j < i; j++)
             if (ss[j] == s) return fail(L, SK_ERR_STATE, "a session appears twice in one batch");
