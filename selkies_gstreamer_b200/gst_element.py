@@ -136,6 +136,15 @@ def element_class():
                        GObject.ParamFlags.READWRITE),
             "add-borders": (GObject.TYPE_BOOLEAN, "add-borders", "videoscale add-borders; only False", False,
                             GObject.ParamFlags.READWRITE),
+            # stock videoconvert properties, accepted only at the values the arithmetic implements
+            "dither": (GObject.TYPE_STRING, "dither", "inert for 8-bit in/out", "bayer", GObject.ParamFlags.READWRITE),
+            "chroma-resampler": (GObject.TYPE_STRING, "chroma-resampler", "only 'linear'", "linear",
+                                 GObject.ParamFlags.READWRITE),
+            "chroma-mode": (GObject.TYPE_STRING, "chroma-mode", "only 'full'", "full", GObject.ParamFlags.READWRITE),
+            "matrix-mode": (GObject.TYPE_STRING, "matrix-mode", "only 'full'", "full", GObject.ParamFlags.READWRITE),
+            "gamma-mode": (GObject.TYPE_STRING, "gamma-mode", "only 'none'", "none", GObject.ParamFlags.READWRITE),
+            "primaries-mode": (GObject.TYPE_STRING, "primaries-mode", "only 'none'", "none",
+                               GObject.ParamFlags.READWRITE),
             "damage": (GObject.TYPE_BOOLEAN, "damage", "produce the per-16x16 damage map", True,
                        GObject.ParamFlags.READWRITE),
             "damage-block-threshold": (GObject.TYPE_UINT, "damage-block-threshold",

@@ -192,6 +192,20 @@ class PreEncodeStage:
         "cuda-device-id": (int, -1, lambda v: v >= -1),              # gstwebrtc_app.py:264-272
         "method": (str, "bilinear", lambda v: v in ("bilinear", 1)),  # videoscale method; only bilinear
         "add-borders": (bool, False, lambda v: v is False),
+        # videoconvert / videoscale properties the reference leaves at their defaults: accepted at the values
+        # the arithmetic implements, refused otherwise (so a mis-set pipeline fails loudly, not subtly)
+        "dither": (str, "bayer", lambda v: v in ("none", "floyd-steinberg", "sierra-lite", "bayer", "verterr")),  # inert at 8 -> 8 bit
+        "dither-quantization": (int, 1, lambda v: v >= 1),
+        "chroma-resampler": (str, "linear", lambda v: v == "linear"),
+        "chroma-mode": (str, "full", lambda v: v == "full"),
+        "matrix-mode": (str, "full", lambda v: v == "full"),
+        "gamma-mode": (str, "none", lambda v: v == "none"),
+        "primaries-mode": (str, "none", lambda v: v == "none"),
+        "alpha-mode": (str, "copy", lambda v: v in ("copy", "set", "mult")),      # no alpha on the output formats
+        "alpha-value": (float, 1.0, lambda v: 0.0 <= v <= 1.0),
+        "sharpness": (float, 1.0, lambda v: v == 1.0),
+        "sharpen": (float, 0.0, lambda v: v == 0.0),
+        "gamma-decode": (bool, False, lambda v: v is False),
         "damage": (bool, True, None),
         "n-inflight": (int, 2, lambda v: 2 <= v <= 8),
         "scale-variant": (int, _abi.SK_SCALE_VARIANT_GST_LQ, lambda v: v in (0, 1)),
@@ -240,6 +254,8 @@ class PreEncodeStage:
             value = float(value)
         if name == "method" and value == 1:
             value = "bilinear"
+        if typ is str and not isinstance(value, str):
+            raise StageError(f"property '{name}' expects a string")
         if check and not check(value):
             raise StageError(f"value {value!r} out of range for property '{name}'")
         with self._lock:

@@ -25,7 +25,7 @@ def test_reference_property_calls_are_accepted():
 def test_property_errors_like_gobject():
     s = PreEncodeStage()
     with pytest.raises(StageError, match="no property named"):
-        s.set_property("dither", 0)
+        s.set_property("brightness", 0)
     with pytest.raises(StageError, match="no property named"):
         s.get_property("nope")
     with pytest.raises(StageError, match="not writable"):
@@ -38,6 +38,21 @@ def test_property_errors_like_gobject():
         s.set_property("add-borders", True)
     with pytest.raises(StageError, match="integer"):
         s.set_property("n-threads", "4")
+
+
+def test_stock_videoconvert_properties_only_at_implemented_values():
+    s = PreEncodeStage()
+    for name, value in (("dither", "none"), ("chroma-resampler", "linear"), ("chroma-mode", "full"),
+                        ("matrix-mode", "full"), ("gamma-mode", "none"), ("primaries-mode", "none"),
+                        ("alpha-mode", "set"), ("alpha-value", 0.5), ("sharpness", 1.0), ("gamma-decode", False)):
+        s.set_property(name, value)
+        assert s.get_property(name) == value
+    for name, value in (("chroma-resampler", "nearest"), ("chroma-mode", "none"), ("matrix-mode", "none"),
+                        ("gamma-mode", "remap"), ("primaries-mode", "fast"), ("sharpness", 1.5), ("gamma-decode", True)):
+        with pytest.raises(StageError, match="out of range"):
+            s.set_property(name, value)
+    with pytest.raises(StageError, match="string"):
+        s.set_property("chroma-mode", 3)
 
 
 def test_caps_parser_roundtrip():
