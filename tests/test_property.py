@@ -16,7 +16,7 @@ MATRIX = ["bt601", "bt709", "bt2020"]
 SITE = ["none", "h-cosited"]
 
 
-@settings(max_examples=60, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@settings(max_examples=60, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow])
 @given(w=even(2, 200), h=even(2, 120), m=st.integers(0, 2), site=st.integers(0, 1), fmt=st.integers(0, 1),
        infmt=st.integers(0, 1), seed=st.integers(0, 2**31 - 1))
 def test_oracle_vs_numpy_random_geometry(w, h, m, site, fmt, infmt, seed):
@@ -27,7 +27,7 @@ def test_oracle_vs_numpy_random_geometry(w, h, m, site, fmt, infmt, seed):
     assert (y == Y).all() and (u == U).all() and (v == V).all()
 
 
-@settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow])
 @given(w=even(4, 160), h=even(4, 100), fx=st.floats(0.3, 1.0), fy=st.floats(0.3, 1.0), var=st.integers(0, 1),
        seed=st.integers(0, 2**31 - 1))
 def test_oracle_scale_vs_numpy_random_geometry(w, h, fx, fy, var, seed):
@@ -41,7 +41,7 @@ def test_oracle_scale_vs_numpy_random_geometry(w, h, fx, fy, var, seed):
 
 
 @pytest.mark.gpu
-@settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
+@settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
 @given(w=even(2, 700), h=even(2, 200), m=st.integers(0, 2), site=st.integers(0, 1), fmt=st.sampled_from(["NV12", "I420"]),
        infmt=st.sampled_from(["BGRx", "RGBx"]), variant=st.integers(0, 15), seed=st.integers(0, 2**31 - 1))
 def test_gpu_convert_random_geometry(w, h, m, site, fmt, infmt, variant, seed):
@@ -70,7 +70,7 @@ def test_gpu_convert_random_geometry(w, h, m, site, fmt, infmt, variant, seed):
 
 
 @pytest.mark.gpu
-@settings(max_examples=40, deadline=None, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
+@settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
 @given(w=even(4, 600), h=even(4, 200), fx=st.floats(0.2, 1.0), fy=st.floats(0.2, 1.0), var=st.integers(0, 1),
        site=st.integers(0, 1), fmt=st.sampled_from(["NV12", "I420"]), generic=st.booleans(), seed=st.integers(0, 2**31 - 1))
 def test_gpu_scale_random_geometry(w, h, fx, fy, var, site, fmt, generic, seed):
