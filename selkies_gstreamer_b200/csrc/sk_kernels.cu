@@ -463,6 +463,57 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
     }
 }
 
+// ---- warp-tile variant of the no-scale kernel ---------------------------------------------
+// One warp owns a whole 256 x 16 tile (16 macroblocks) and walks its 8 row pairs in a loop, so the
+// damage flags never leave the warp: no shared memory, no __syncthreads, and a CTA lives 8x longer.
+template <int FMT, int SITE, bool DAMAGE, bool POLICY>
+__global__ void __launch_bounds__(kThreads, 5)
+sk_convert_warp_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+{
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int tiles_x = (g.out_w + 255) / 256;
+    const int tiles = tiles_x * ((g.out_h + 15) / 16);
+    int wid = blockIdx.x * 8 + warp;                    // this warp's tile within the frame
+    if (wid >= tiles) return;                           // no block-wide barrier below
+    const unsigned biz = g.reverse ? gridDim.z - 1 - blockIdx.z : blockIdx.z;
+    if (g.reverse) wid = tiles - 1 - wid;
+    const SkFrame &f = batch.f[biz];
+    const int tx = wid % tiles_x, ty = wid / tiles_x;
+    const int bx0 = tx * 256, by0 = ty * 16;
+    const bool have_prev = DAMAGE && (f.prev != nullptr);
+    const bool full = (bx0 + 256 <= g.out_w) && (by0 + 16 <= g.out_h);
+
+    uint32_t pol_state = 0;
+    if (DAMAGE && POLICY) pol_state = policy_prefetch(f, g, lane < 16, tx * 16 + lane, ty);
+
+    uint32_t acc[2] = {0, 0};
+    int nvq[2] = {0, 0};
+#pragma unroll 1
+    for (int it = 0; it < 8; it++) {
+        uint32_t d[2];
+        const int y0 = by0 + 2 * it;
+        if (full) convert_tile<1, 2, FMT, SITE, DAMAGE, 0, true>(g, f, bx0, y0, lane, have_prev, d, nvq);
+        else      convert_tile<1, 2, FMT, SITE, DAMAGE, 0, false>(g, f, bx0, y0, lane, have_prev, d, nvq);
+        acc[0] |= d[0];
+        acc[1] |= d[1];
+    }
+    if (DAMAGE) {
+        // 4 adjacent lanes = one macroblock; lanes 0..7 publish the blocks of q = 0, lanes 8..15 those of q = 1
+        const uint32_t m0 = __ballot_sync(kFull, nvq[0] > 0 && (acc[0] != 0 || !have_prev));
+        const uint32_t m1 = __ballot_sync(kFull, nvq[1] > 0 && (acc[1] != 0 || !have_prev));
+        if (lane < 16) {
+            const uint32_t m = lane < 8 ? m0 : m1;
+            const bool flag = ((m >> (4 * (lane & 7))) & 0xfu) != 0;
+            const int bx = tx * 16 + lane;
+            if (bx < g.mb_w && ty < g.mb_h) {
+                f.map[(size_t)ty * g.mb_w + bx] = flag ? 1 : 0;
+                if (POLICY) policy_update(f, g, (size_t)ty * g.mb_w + bx, flag, pol_state);
+            }
+        }
+    }
+}
+
 // ---- scale kernel ---------------------------------------------------------------
 // 2-tap shrink in the RGB domain before the matrix (order as upstream's
 // chain_scale: h first when out_w*in_h <= in_w*out_h), then the same
@@ -932,6 +983,24 @@ cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaS
     return cudaErrorInvalidValue;
 }
 
+cudaError_t launch_convert_warp(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
+{
+    const int tiles = ((g.out_w + 255) / 256) * ((g.out_h + 15) / 16);
+    dim3 grid((tiles + 7) / 8, 1, n);
+    dim3 block(kThreads);
+    const bool policy = g.damage != 0 && b.f[0].state != nullptr;
+#define SK_CASE(FMT, SITE, DMG)                                                                        \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                                 \
+        if (DMG && policy) sk_convert_warp_kernel<FMT, SITE, DMG, DMG><<<grid, block, 0, st>>>(g, b);   \
+        else sk_convert_warp_kernel<FMT, SITE, DMG, false><<<grid, block, 0, st>>>(g, b);               \
+        return cudaGetLastError();                                                                    \
+    }
+    SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
+    SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
+#undef SK_CASE
+    return cudaErrorInvalidValue;
+}
+
 }  // namespace
 
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant)
@@ -952,7 +1021,7 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
     case 9: return launch_convert_shape<4, 2, 0>(g, b, n, st);
     case 10: return launch_convert_shape<2, 4, 0>(g, b, n, st);
     case 11: return launch_convert_shape<1, 4, 0>(g, b, n, st);
-    case 12: return launch_convert_shape<1, 2, 2>(g, b, n, st);   // default shape, streaming stores
+    case 12: return launch_convert_warp(g, b, n, st);             // one warp per 256x16 tile, no shared memory / barriers
     case 13: return launch_convert_shape<1, 2, 3>(g, b, n, st);   // default shape, streaming loads + stores
     case 14: return launch_convert_shape<1, 2, 4>(g, b, n, st);   // default shape, input rows staged by cp.async.bulk (TMA engine)
     }
