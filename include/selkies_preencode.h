@@ -114,7 +114,7 @@ typedef struct sk_result {
     const uint8_t *host_damage_map; /* pinned, uint8[mb_h][mb_w], 1 = damaged; NULL if NO_DAMAGE  */
     const uint8_t *dev_damage_map;
     int32_t  mb_w, mb_h;
-    uint32_t damaged_count;       /* exact sum of the map (added up on the host in sk_wait)        */
+    uint32_t damaged_count;       /* exact sum of the map (reduced on the GPU with the map)        */
     float    h2d_us, kernel_us, d2h_us;   /* only with SK_FLAG_TIMING                             */
     const uint8_t *host_policy_map; /* pinned, uint8[mb_h][mb_w] of SK_POLICY_* bits; NULL without SK_FLAG_POLICY */
     const uint8_t *dev_policy_map;

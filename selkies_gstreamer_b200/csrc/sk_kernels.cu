@@ -441,6 +441,7 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
         }
         __syncthreads();
         constexpr int WPM = 8 / RP;                 // warps per macroblock row
+        bool hit = false;
         if (threadIdx.x < NMB) {
             const int t = threadIdx.x;
             const int mbrow = t / (QX * 8);
@@ -456,10 +457,14 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
             if (bx < g.mb_w && by < g.mb_h) {
                 f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
                 if (POLICY) policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
+                hit = flag;
             }
         }
-        // no device-wide count here: a returning atomic on every CTA's tail keeps the CTA's registers
-        // allocated for ~1 us (4.7 % of the kernel rate in the A/B run); the session sums the map on the host
+        // Block count by the barrier itself, then ONE fire-and-forget atomic (RED) per CTA into a word the
+        // host zeroed before the launch.  (A returning atomic here — the ticket scheme of finish_count —
+        // kept every CTA's registers allocated ~1 us longer and cost 4.7 % of the kernel rate.)
+        const int total = __syncthreads_count(hit);
+        if (threadIdx.x == 0 && total != 0 && f.count_out != nullptr) atomicAdd(f.count_out, (uint32_t)total);
     }
 }
 
@@ -502,6 +507,7 @@ sk_convert_warp_kernel(const __grid_constant__ SkGeom g, const __grid_constant__
         // 4 adjacent lanes = one macroblock; lanes 0..7 publish the blocks of q = 0, lanes 8..15 those of q = 1
         const uint32_t m0 = __ballot_sync(kFull, nvq[0] > 0 && (acc[0] != 0 || !have_prev));
         const uint32_t m1 = __ballot_sync(kFull, nvq[1] > 0 && (acc[1] != 0 || !have_prev));
+        bool hit = false;
         if (lane < 16) {
             const uint32_t m = lane < 8 ? m0 : m1;
             const bool flag = ((m >> (4 * (lane & 7))) & 0xfu) != 0;
@@ -509,8 +515,11 @@ sk_convert_warp_kernel(const __grid_constant__ SkGeom g, const __grid_constant__
             if (bx < g.mb_w && ty < g.mb_h) {
                 f.map[(size_t)ty * g.mb_w + bx] = flag ? 1 : 0;
                 if (POLICY) policy_update(f, g, (size_t)ty * g.mb_w + bx, flag, pol_state);
+                hit = flag;
             }
         }
+        const uint32_t votes = __ballot_sync(kFull, hit);
+        if (lane == 0 && votes != 0 && f.count_out != nullptr) atomicAdd(f.count_out, (uint32_t)__popc(votes));
     }
 }
 
@@ -675,7 +684,10 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
                 }
             }
             uint32_t votes = __ballot_sync(kFull, valid && flag);
-            if (lane == 0 && f.scratch != nullptr) finish_count(f, (uint32_t)__popc(votes));
+            if (lane == 0) {
+                if (f.scratch != nullptr) finish_count(f, (uint32_t)__popc(votes));      // allocation-free entry point
+                else if (votes != 0 && f.count_out != nullptr) atomicAdd(f.count_out, (uint32_t)__popc(votes));
+            }
         }
     }
 }
@@ -949,6 +961,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
         uint32_t m = __ballot_sync(kFull, d);
         if (lane == 0) s_mask[warp] = m;
         __syncthreads();
+        bool hit = false;
         if (threadIdx.x < 8) {
             uint32_t acc = 0;
 #pragma unroll
@@ -958,10 +971,14 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
             if (bx < g.mb_w && by < g.mb_h) {
                 f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
                 policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
+                hit = flag;
             }
         }
-        // no device-wide count here: a returning atomic on every CTA's tail keeps the CTA's registers
-        // allocated for ~1 us (4.7 % of the kernel rate in the A/B run); the session sums the map on the host
+        // Block count by the barrier itself, then ONE fire-and-forget atomic (RED) per CTA into a word the
+        // host zeroed before the launch.  (A returning atomic here — the ticket scheme of finish_count —
+        // kept every CTA's registers allocated ~1 us longer and cost 4.7 % of the kernel rate.)
+        const int total = __syncthreads_count(hit);
+        if (threadIdx.x == 0 && total != 0 && f.count_out != nullptr) atomicAdd(f.count_out, (uint32_t)total);
     }
 }
 

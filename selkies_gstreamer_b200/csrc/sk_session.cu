@@ -26,6 +26,7 @@
 namespace {
 
 constexpr int kMaxInflight = 8;
+constexpr size_t kCountHdr = 128;      // counts (one u32 per batch member) in front of the maps of a meta block
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_variant{0};
 std::atomic<int> g_snake{1};            // alternate traversal direction per launch (102 off / 103 on)
@@ -33,27 +34,6 @@ std::atomic<int> g_scale_generic{0};   // tuning/testing: force the generic scal
 thread_local std::string g_create_error;
 
 using skhost::ru;
-
-// Sum of n bytes that are each 0 or 1: eight at a time, folding before a lane can overflow.
-uint32_t sum_bytes(const uint8_t *p, size_t n)
-{
-    uint64_t total = 0;
-    size_t i = 0;
-    while (i + 8 <= n) {
-        uint64_t acc = 0;
-        const size_t stop = (n - i) / 8 < 255 ? i + (n - i) / 8 * 8 : i + 255 * 8;
-        for (; i < stop; i += 8) {
-            uint64_t v;
-            std::memcpy(&v, p + i, 8);
-            acc += v;
-        }
-        acc = (acc & 0x00ff00ff00ff00ffull) + ((acc >> 8) & 0x00ff00ff00ff00ffull);
-        acc = (acc & 0x0000ffff0000ffffull) + ((acc >> 16) & 0x0000ffff0000ffffull);
-        total += (acc & 0xffffffffull) + (acc >> 32);
-    }
-    for (; i < n; i++) total += p[i];
-    return (uint32_t)total;
-}
 
 struct Slot {          // one staging slot (caller-chosen index)
     uint8_t *h_in = nullptr;
@@ -77,8 +57,7 @@ struct Ring {          // one output ring entry (submission order)
     bool valid = false;
     bool had_h2d = false;
     bool used = false;                // `done` has been recorded at least once
-    uint32_t count = 0;               // damaged blocks of this frame (host sum of the map)
-    bool count_valid = false;
+    const uint32_t *h_count = nullptr; // this frame's damaged-block count in pinned memory
 };
 
 }  // namespace
@@ -205,18 +184,19 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.in = in;
     f.out = r.d_out;
     f.prev = (s->prev_ring >= 0) ? s->ring[s->prev_ring].d_out : nullptr;
-    r.d_meta_view = r.d_meta;
-    r.h_meta_view = r.h_meta;
-    f.map = r.d_meta;
-    f.count_out = nullptr;                      // sessions count on the host (sk_wait)
+    r.d_meta_view = r.d_meta + kCountHdr;
+    r.h_meta_view = r.h_meta + kCountHdr;
+    r.h_count = reinterpret_cast<const uint32_t *>(r.h_meta);
+    f.map = r.d_meta_view;
+    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta);     // zeroed on the stream before the launch
     f.state = s->d_state;                       // nullptr unless SK_FLAG_POLICY
-    f.policy = r.d_meta + s->map_bytes;
+    f.policy = r.d_meta_view + s->map_bytes;
     f.scratch = nullptr;
     f.v_off = s->d_voff;
     f.v_tap = s->d_vtap;
     r.frame_id = frame_id;
     r.valid = true;
-    r.count_valid = false;
+
     s->prev_ring = ri;
     s->seq++;
     return ri;
@@ -241,7 +221,7 @@ int enqueue_readback(sk_session *s, int ri, cudaEvent_t kernel_done)
     SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, kernel_done, 0));
     if (timing) SK_CUDA(s, cudaEventRecord(r.d2h_start, s->s_d2h));
     if (damage)
-        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, s->d_state ? s->meta_bytes : s->map_bytes,
+        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, kCountHdr + (s->d_state ? s->meta_bytes : s->map_bytes),
                                    cudaMemcpyDeviceToHost, s->s_d2h));
     if (host_out)
         SK_CUDA(s, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
@@ -266,6 +246,7 @@ int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot,
 
     SkBatch b;
     const int ri = stage_frame(s, d_in, frame_id, b.f[0]);
+    if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) SK_CUDA(s, cudaMemsetAsync(r.d_meta, 0, 4, s->s_comp));
     if (timing) SK_CUDA(s, cudaEventRecord(r.k_start, s->s_comp));
     SK_CUDA(s, launch(s, g, b, 1, s->s_comp));
     SK_CUDA(s, cudaEventRecord(r.k_done, s->s_comp));
@@ -389,10 +370,10 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         Ring &r = s->ring[i];
         SK_TRY(cudaMalloc((void **)&r.d_out, s->frame_bytes));
         SK_TRY(cudaMemset(r.d_out, 0, s->frame_bytes));
-        SK_TRY(cudaMalloc((void **)&r.d_meta, s->meta_bytes));
-        SK_TRY(cudaMemset(r.d_meta, 0, s->meta_bytes));
-        SK_TRY(cudaHostAlloc((void **)&r.h_meta, s->meta_bytes, cudaHostAllocDefault));
-        std::memset(r.h_meta, 0, s->meta_bytes);
+        SK_TRY(cudaMalloc((void **)&r.d_meta, kCountHdr + s->meta_bytes));
+        SK_TRY(cudaMemset(r.d_meta, 0, kCountHdr + s->meta_bytes));
+        SK_TRY(cudaHostAlloc((void **)&r.h_meta, kCountHdr + s->meta_bytes, cudaHostAllocDefault));
+        std::memset(r.h_meta, 0, kCountHdr + s->meta_bytes);
         if (c.flags & SK_FLAG_HOST_OUTPUT)
             SK_TRY(cudaHostAlloc((void **)&r.h_out, s->frame_bytes, cudaHostAllocDefault));
         cudaEvent_t *evs[] = {&r.h2d_start, &r.h2d_done, &r.k_start, &r.k_done, &r.d2h_start, &r.done};
@@ -626,17 +607,20 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
         // read-back is ONE copy per step instead of one small copy per session.
         const int lri = ris[0];
         if (!L->d_bmeta[lri]) {
-            SK_CUDA(L, cudaMalloc((void **)&L->d_bmeta[lri], (size_t)SK_MAX_BATCH * L->meta_bytes));
-            SK_CUDA(L, cudaHostAlloc((void **)&L->h_bmeta[lri], (size_t)SK_MAX_BATCH * L->meta_bytes, cudaHostAllocDefault));
+            SK_CUDA(L, cudaMalloc((void **)&L->d_bmeta[lri], kCountHdr + (size_t)SK_MAX_BATCH * L->meta_bytes));
+            SK_CUDA(L, cudaHostAlloc((void **)&L->h_bmeta[lri], kCountHdr + (size_t)SK_MAX_BATCH * L->meta_bytes, cudaHostAllocDefault));
         }
         for (int i = 0; i < n; i++) {
             Ring &r = ss[i]->ring[ris[i]];
-            r.d_meta_view = L->d_bmeta[lri] + (size_t)i * L->meta_bytes;
-            r.h_meta_view = L->h_bmeta[lri] + (size_t)i * L->meta_bytes;
+            r.d_meta_view = L->d_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
+            r.h_meta_view = L->h_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
+            r.h_count = reinterpret_cast<const uint32_t *>(L->h_bmeta[lri]) + i;
+            b.f[i].count_out = reinterpret_cast<uint32_t *>(L->d_bmeta[lri]) + i;
             b.f[i].map = r.d_meta_view;
             b.f[i].policy = r.d_meta_view + L->map_bytes;
         }
     }
+    if (damage) SK_CUDA(L, cudaMemsetAsync(L->d_bmeta[ris[0]], 0, kCountHdr, L->s_comp));
     if (timing) SK_CUDA(L, cudaEventRecord(lr.k_start, L->s_comp));
     SK_CUDA(L, launch(L, g, b, n, L->s_comp));
     SK_CUDA(L, cudaEventRecord(lr.k_done, L->s_comp));
@@ -644,7 +628,7 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
     SK_CUDA(L, cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
     if (timing) SK_CUDA(L, cudaEventRecord(lr.d2h_start, L->s_d2h));
     if (damage)
-        SK_CUDA(L, cudaMemcpyAsync(L->h_bmeta[ris[0]], L->d_bmeta[ris[0]], (size_t)n * L->meta_bytes,
+        SK_CUDA(L, cudaMemcpyAsync(L->h_bmeta[ris[0]], L->d_bmeta[ris[0]], kCountHdr + (size_t)n * L->meta_bytes,
                                    cudaMemcpyDeviceToHost, L->s_d2h));
     for (int i = 0; i < n; i++) {
         sk_session *s = ss[i];
@@ -694,11 +678,7 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
         if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) {
             out->host_damage_map = r.h_meta_view;
             out->dev_damage_map = r.d_meta_view;
-            if (!r.count_valid) {                 // exact sum of the 0/1 map bytes, once per frame
-                r.count = sum_bytes(r.h_meta_view, (size_t)s->geom.mb_w * s->geom.mb_h);
-                r.count_valid = true;
-            }
-            out->damaged_count = r.count;
+            out->damaged_count = *r.h_count;
             if (s->d_state) {
                 out->host_policy_map = r.h_meta_view + s->map_bytes;
                 out->dev_policy_map = r.d_meta_view + s->map_bytes;
@@ -744,11 +724,7 @@ int sk_batch_wait(sk_session **ss, int n, uint64_t frame_id, uint32_t *damaged_c
             damaged_counts[i] = res.damaged_count;
             continue;
         }
-        if (!r.count_valid) {
-            r.count = sum_bytes(r.h_meta_view, (size_t)s->geom.mb_w * s->geom.mb_h);
-            r.count_valid = true;
-        }
-        damaged_counts[i] = r.count;
+        damaged_counts[i] = *r.h_count;
     }
     return SK_OK;
 }
