@@ -251,6 +251,22 @@ def test_scale_parity(dims, variant, kernel):
         lib.sk_set_kernel_variant(101)
 
 
+@pytest.mark.parametrize("dims", [(128, 64, 64, 96), (64, 128, 96, 64), (200, 100, 100, 150), (100, 200, 160, 100)])
+@pytest.mark.parametrize("kernel", ["tiled", "generic"])
+def test_scale_one_axis_enlarging_with_fewer_pixels(dims, kernel):
+    """Fewer output than input pixels, but one axis grows: still the scale-before-matrix chain."""
+    w, h, ow, oh = dims
+    f0 = rand_frame(w, h, w + oh)
+    f1 = synth.mutate(f0, 0.1, seed=3, aligned=False)
+    lib = _abi.load()
+    try:
+        lib.sk_set_kernel_variant(100 if kernel == "generic" else 101)
+        for out_format, site in (("I420", 1), ("NV12", 0)):
+            check_sequence([f0, f1], w, h, out_w=ow, out_h=oh, out_format=out_format, chroma_site=site)
+    finally:
+        lib.sk_set_kernel_variant(101)
+
+
 @pytest.mark.parametrize("dims", [(1366, 768, 1280, 720), (258, 130, 130, 66), (2560, 1440, 1278, 720), (514, 96, 258, 90)])
 def test_scale_ragged_edges(dims):
     w, h, ow, oh = dims
