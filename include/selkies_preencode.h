@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SK_ABI_VERSION 2
+#define SK_ABI_VERSION 3
 
 /* status codes */
 enum {
@@ -65,8 +65,19 @@ enum {
     SK_FLAG_NO_DAMAGE   = 1 << 0,  /* convert-only: no previous-frame read, no map                   */
     SK_FLAG_HOST_OUTPUT = 1 << 1,  /* copy the converted frame back to pinned host memory each frame */
     SK_FLAG_TIMING      = 1 << 2,  /* record CUDA events; sk_result.*_us are filled                  */
-    SK_FLAG_POLICY      = 1 << 3   /* keep per-macroblock temporal counters in the kernel and return
+    SK_FLAG_POLICY      = 1 << 3,  /* keep per-macroblock temporal counters in the kernel and return
                                       the SK_POLICY_* map (hot / paint-over), see below              */
+    SK_FLAG_SCALE_GENERIC = 1 << 4, /* scale with the gather kernel even where the shared-memory tiled
+                                      kernel applies (A/B measurements, tests); results are identical  */
+    SK_FLAG_SPIN_WAIT   = 1 << 5,  /* sk_wait busy-polls (lowest latency, burns one host core).  Default:
+                                      the waiting thread sleeps (cudaEventBlockingSync) — this stage exists
+                                      to take load OFF the host cores (docs/design.md:33)               */
+    SK_FLAG_GATED_READBACK = 1 << 6 /* with SK_FLAG_HOST_OUTPUT: sk_result.host_frame is a persistent pinned
+                                      frame per ring entry into which only the macroblocks that changed
+                                      since that copy was last refreshed are written (zero-copy stores
+                                      from the GPU) — a mostly static desktop (BASELINE.json config 5)
+                                      sends a few KB back instead of the whole frame.  Not with batches
+                                      or a caller-supplied output buffer.                               */
 };
 
 typedef struct sk_session sk_session;
@@ -118,6 +129,9 @@ typedef struct sk_result {
     float    h2d_us, kernel_us, d2h_us;   /* only with SK_FLAG_TIMING                             */
     const uint8_t *host_policy_map; /* pinned, uint8[mb_h][mb_w] of SK_POLICY_* bits; NULL without SK_FLAG_POLICY */
     const uint8_t *dev_policy_map;
+    const uint32_t *dev_damaged_count; /* the count word in HBM (what a device-side consumer reads)    */
+    uint64_t readback_bytes;      /* frame bytes that crossed PCIe for host_frame: frame_bytes, or with
+                                     SK_FLAG_GATED_READBACK 384 B per macroblock actually written     */
 } sk_result;
 
 /* Replaces: Gst.ElementFactory.make("videoconvert"/"cudaconvert") + set_caps
@@ -156,6 +170,15 @@ int sk_submit(sk_session *s, int slot, uint64_t frame_id);
  * unchanged until sk_wait(frame_id) returns. */
 int sk_submit_host(sk_session *s, int slot, const void *host_ptr, size_t stride, uint64_t frame_id);
 
+/* Same as sk_submit_host, and the converted frame is copied back INTO THE CALLER'S buffer
+ * `host_out` (frame_bytes of it; NULL = as configured by SK_FLAG_HOST_OUTPUT) instead of the
+ * library's pinned ring: the GstBuffer a GstBaseTransform hands to transform() as `outbuf`
+ * (upstream; the reference's pipeline links the stage's src pad to the encoder at
+ * gstwebrtc_app.py:991-994).  sk_result.host_frame is then host_out.  Pin recycled pool buffers
+ * once with sk_host_register so both copies are asynchronous DMA without a host-side memcpy. */
+int sk_submit_io(sk_session *s, int slot, const void *host_in, size_t in_stride, void *host_out,
+                 uint64_t frame_id);
+
 /* Pin / unpin a caller-owned capture buffer (e.g. the XShm segment) for sk_submit_host.
  * Pinning costs milliseconds: do it once per buffer, not per frame. */
 int sk_host_register(void *ptr, size_t bytes);
@@ -168,6 +191,27 @@ int sk_submit_device(sk_session *s, const void *dptr, size_t stride, uint64_t fr
 
 /* Block until frame_id is complete and describe it. */
 int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out);
+
+/* Copy the converted frame of frame_id from HBM into `host_out` (frame_bytes) and block until it is
+ * there — for sessions without SK_FLAG_HOST_OUTPUT whose host occasionally does need the pixels
+ * (a screenshot, a checker), while the ring entry is still valid.  The reference has no
+ * counterpart: its stage always hands the whole frame downstream (gstwebrtc_app.py:991-994). */
+int sk_read_frame(sk_session *s, uint64_t frame_id, void *host_out);
+
+/* Device-side completion for consumers that stay on the GPU — the reference's primary branch:
+ * `video/x-raw(memory:CUDAMemory),format=NV12` into nvh264enc / nvh265enc / nvav1enc
+ * (gstwebrtc_app.py:281-284, :286-367, :370-380, :427-437).  Makes `cuda_stream` (a cudaStream_t of
+ * the session's device) wait for the kernel that produced frame_id; the host does not block and no
+ * frame D2H is needed (create the session without SK_FLAG_HOST_OUTPUT).  `out` receives the device
+ * pointers (dev_frame, dev_damage_map, dev_policy_map, dev_damaged_count, layout); its host_*
+ * fields are NULL and damaged_count is 0 — use sk_wait for the host copies of map and count. */
+int sk_wait_device(sk_session *s, uint64_t frame_id, void *cuda_stream, sk_result *out);
+
+/* The consumer's half of that contract: call after queueing the last read of frame_id's device
+ * buffers on `cuda_stream`.  The ring entry is not overwritten (n_inflight frames later) before the
+ * work queued on cuda_stream up to this point has finished.  Without this call the ring depth alone
+ * protects the consumer, as for sk_wait. */
+int sk_release_device(sk_session *s, uint64_t frame_id, void *cuda_stream);
 
 /* Next frame is treated as having no predecessor: map = all ones.  Replaces the
  * renegotiation after a resize (src/selkies/legacy/webrtc_input.py:672-678 →
@@ -182,6 +226,22 @@ int sk_reset_history(sk_session *s);
  * batch together, after the last batch has been waited for. */
 int sk_batch_submit(sk_session **sessions, int n, const void *const *dptrs,
                     size_t stride, uint64_t frame_id);
+
+/* Allocate the batch bookkeeping of a group led by sessions[0] (one contiguous map block per ring
+ * entry) ahead of time, so that no later sk_batch_submit* allocates on the frame path.  Optional:
+ * the first sk_batch_submit of a leader does the same, before anything is queued. */
+int sk_batch_prepare(sk_session **sessions, int n);
+
+/* sk_batch_submit for frames that are still in HOST memory — what N stage instances of one process
+ * hand over when their transform() calls arrive together (the reference builds several apps per
+ * process, src/selkies/legacy/webrtc.py:684-685; stage call sites gstwebrtc_app.py:611-617):
+ * every member's frame goes up on that member's own copy stream (host_in[i], rows in_stride apart,
+ * 0 = tight; pinned or registered memory is asynchronous DMA), then ONE launch converts all of them,
+ * then the frames come back — into host_out[i] when host_out and host_out[i] are non-NULL, else as
+ * the member's SK_FLAG_HOST_OUTPUT says.  Membership may change from call to call.  Each member's
+ * maps land in its own meta buffers.  Completion via sk_wait on each member (or sk_batch_wait). */
+int sk_batch_submit_host(sk_session **sessions, int n, const void *const *host_in, size_t in_stride,
+                         void *const *host_out, uint64_t frame_id);
 
 /* Wait for frame_id on every session of a batch; damaged_counts (may be NULL)
  * receives one exact count per session.  Maps stay readable through sk_wait. */
@@ -198,6 +258,15 @@ int sk_last_kernel_us(sk_session *s, float *us);
 int sk_marker_record(sk_session *s, int which);
 int sk_marker_elapsed_us(sk_session *s, float *us);
 
+/* Measurement helper: the bare PCIe rate of this process's GPU `device_id`, with nothing of the
+ * session machinery involved — `iters` back-to-back cudaMemcpyAsync of `bytes` between one pinned
+ * host buffer and one device buffer, timed with CUDA events.  mode 0: host->device only,
+ * 1: device->host only, 2: both directions at once on two streams.  The rates (GB/s, 0 when the
+ * direction was not exercised) are what the frame path's copies are judged against
+ * (north_star: "the H2D copy is reported separately against PCIe bandwidth"; the reference has
+ * no such probe).  Allocates and frees its own buffers: not for the frame path. */
+int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_gbs, double *d2h_gbs);
+
 /*
  * Convert (and shrink) ONE frame on buffers the caller owns, without allocating anything.
  * This entry point has no counterpart in the reference.
@@ -209,12 +278,14 @@ int sk_marker_elapsed_us(sk_session *s, float *us);
  * caching allocator) and is fully handed out.  No cudaMalloc, cudaFree or other allocating
  * call is made here, on any path.
  *
- * The kernel is the shrink+convert+damage kernel of the session path (equal sizes are
- * allowed).  Its scratch — the two reduction words of the damage count and one vertical
- * tap entry per output row — lives in a fixed array inside the library image, about 26 KB
- * on every GPU that loads the library, for the life of the process.  Hence the limit:
- * out_height <= SK_NOALLOC_MAX_OUT_HEIGHT, anything taller is refused with SK_ERR_ARG
- * and a message in errbuf (use a session for it).
+ * The kernel is the library's generic scale kernel (every output pixel gathers its own taps
+ * through L1; equal sizes are allowed and then it simply converts) — NOT the shared-memory tiled
+ * kernel a session normally runs, which needs per-session set-up.  Output is bit-identical to a
+ * session's; it is about 1.7x slower per frame (profiles/r2_noalloc_timing.md).  Its scratch — the
+ * two reduction words of the damage count and one vertical tap entry per output row — lives in a
+ * fixed array inside the library image, about 26 KB on every GPU that loads the library, for the
+ * life of the process.  Hence the limit: out_height <= SK_NOALLOC_MAX_OUT_HEIGHT, anything taller
+ * is refused with SK_ERR_ARG and a message in errbuf (use a session for it).
  *
  *   cfg        geometry, formats, matrix, chroma_site, scale_variant, SK_FLAG_NO_DAMAGE as
  *              for sk_session_create; device_id < 0 means the calling thread's current
@@ -228,8 +299,11 @@ int sk_marker_elapsed_us(sk_session *s, float *us);
  *   errbuf     optional buffer for a human-readable error, errbuf_len bytes
  * All device pointers and in_stride must be 4-byte aligned.
  *
- * The first call on each GPU looks up where that GPU keeps the array
- * (cudaGetSymbolAddress); make that first call before starting any stream capture.
+ * The first call on each GPU looks up where that GPU keeps the array (cudaGetSymbolAddress) and
+ * loads all eight instantiations of the kernel into that GPU's context, so that later calls with
+ * another format / chroma site do not trigger a lazy code load; make that first call before
+ * starting any stream capture.  When in_height != out_height the tap entries are uploaded from a
+ * static host table that every call rewrites.
  * All calls share the one array, which still holds what the previous call left there;
  * each call re-zeroes the reduction words and rewrites the tap entries on cuda_stream
  * before its kernel.  Two calls whose GPU work can overlap (different streams, or
@@ -252,9 +326,6 @@ int sk_version(void);
 
 /* Number of CUDA devices visible (0 on a CPU-only host; never fails). */
 int sk_device_count(void);
-
-/* Kernel-variant selector for tuning runs (0 = library default); process-wide. */
-int sk_set_kernel_variant(int variant);
 
 #ifdef __cplusplus
 }

@@ -23,17 +23,20 @@ SK_SITE_NONE, SK_SITE_H_COSITED = 0, 1
 SK_SCALE_BILINEAR = 1
 SK_SCALE_VARIANT_GST_LQ, SK_SCALE_VARIANT_PLAIN_LQ = 0, 1
 SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING, SK_FLAG_POLICY = 1, 2, 4, 8
+SK_FLAG_SCALE_GENERIC, SK_FLAG_SPIN_WAIT, SK_FLAG_GATED_READBACK = 16, 32, 64
 SK_MAX_BATCH = 32
-SK_ABI_VERSION = 2
+SK_ABI_VERSION = 3
 SK_POLICY_DAMAGED, SK_POLICY_HOT, SK_POLICY_PAINT_OVER = 1, 2, 4
 SK_NOALLOC_MAX_OUT_HEIGHT = 4320
 
 # Every symbol include/selkies_preencode.h declares (tests check the .so exports all of them).
 EXPORTS = (
     "sk_session_create", "sk_session_destroy", "sk_get_input_staging", "sk_get_device_input",
-    "sk_upload", "sk_submit", "sk_submit_host", "sk_host_register", "sk_host_unregister", "sk_submit_device", "sk_wait", "sk_reset_history",
-    "sk_batch_submit", "sk_batch_wait", "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us",
-    "sk_scale_frame_noalloc", "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count", "sk_set_kernel_variant",
+    "sk_upload", "sk_submit", "sk_submit_host", "sk_submit_io", "sk_host_register", "sk_host_unregister", "sk_submit_device",
+    "sk_wait", "sk_read_frame", "sk_wait_device", "sk_release_device", "sk_reset_history",
+    "sk_batch_prepare", "sk_batch_submit", "sk_batch_submit_host", "sk_batch_wait",
+    "sk_last_kernel_us", "sk_marker_record", "sk_marker_elapsed_us", "sk_pcie_probe",
+    "sk_scale_frame_noalloc", "sk_launch_count", "sk_last_error", "sk_version", "sk_device_count",
 )
 
 
@@ -73,6 +76,8 @@ class SkResult(ctypes.Structure):
         ("h2d_us", ctypes.c_float), ("kernel_us", ctypes.c_float), ("d2h_us", ctypes.c_float),
         ("host_policy_map", ctypes.c_void_p),
         ("dev_policy_map", ctypes.c_void_p),
+        ("dev_damaged_count", ctypes.c_void_p),
+        ("readback_bytes", ctypes.c_uint64),
     ]
 
 
@@ -115,22 +120,28 @@ def load() -> ctypes.CDLL:
         "sk_upload": (i, [vp, i, vp, sz]),
         "sk_submit": (i, [vp, i, u64]),
         "sk_submit_host": (i, [vp, i, vp, sz, u64]),
+        "sk_submit_io": (i, [vp, i, vp, sz, vp, u64]),
         "sk_host_register": (i, [vp, sz]),
         "sk_host_unregister": (i, [vp]),
         "sk_submit_device": (i, [vp, vp, sz, u64]),
         "sk_wait": (i, [vp, u64, ctypes.POINTER(SkResult)]),
+        "sk_read_frame": (i, [vp, u64, vp]),
+        "sk_wait_device": (i, [vp, u64, vp, ctypes.POINTER(SkResult)]),
+        "sk_release_device": (i, [vp, u64, vp]),
         "sk_reset_history": (i, [vp]),
+        "sk_batch_prepare": (i, [vpp, i]),
         "sk_batch_submit": (i, [vpp, i, vpp, sz, u64]),
+        "sk_batch_submit_host": (i, [vpp, i, vpp, sz, vpp, u64]),
         "sk_batch_wait": (i, [vpp, i, u64, ctypes.POINTER(ctypes.c_uint32)]),
         "sk_last_kernel_us": (i, [vp, fp]),
         "sk_marker_record": (i, [vp, i]),
         "sk_marker_elapsed_us": (i, [vp, fp]),
+        "sk_pcie_probe": (i, [i, sz, i, i, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_double)]),
         "sk_scale_frame_noalloc": (i, [ctypes.POINTER(SkConfig), vp, sz, vp, vp, vp, vp, vp, ctypes.c_char_p, sz]),
         "sk_launch_count": (u64, []),
         "sk_last_error": (ctypes.c_char_p, [vp]),
         "sk_version": (i, []),
         "sk_device_count": (i, []),
-        "sk_set_kernel_variant": (i, [i]),
     }
     assert set(protos) == set(EXPORTS)
     for name, (res, args) in protos.items():
@@ -140,6 +151,11 @@ def load() -> ctypes.CDLL:
             raise PreencodeLibraryError(f"{LIB_PATH} does not export {name}; rebuild it") from e
         fn.restype = res
         fn.argtypes = args
+    # The tuning build (make -C csrc tuning, selected with SELKIES_PREENCODE_LIB) also carries the
+    # kernel-shape selector of the round-1 sweep; it is not part of the public header.
+    if hasattr(L, "sk_tuning_set_variant"):
+        L.sk_tuning_set_variant.restype = i
+        L.sk_tuning_set_variant.argtypes = [i]
     if L.sk_version() != SK_ABI_VERSION:
         raise PreencodeLibraryError(f"ABI version mismatch: library {L.sk_version()}, binding {SK_ABI_VERSION}")
     _lib = L

@@ -982,6 +982,82 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     }
 }
 
+// ---- damage-gated read-back ------------------------------------------------------------
+// System-memory consumers need the converted frame on the host, but on a desktop most of it did not
+// change.  Instead of a full-frame D2H the macroblocks whose map byte is set are written straight
+// into a persistent frame in mapped pinned host memory (zero-copy stores over PCIe): thread = one
+// macroblock column of one macroblock row, so adjacent damaged blocks become contiguous 16-byte-per-lane
+// warp stores.  The host frame of ring entry k was last refreshed n_ring frames ago: `stale[j]` keeps,
+// per host frame j, the union of the maps it has missed; entry k copies map|stale[k] and clears it,
+// the others accumulate this frame's map.
+template <int FMT, bool VEC>
+__global__ void __launch_bounds__(kThreads)
+sk_gather_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkGather a)
+{
+    const int bx = blockIdx.x * kThreads + threadIdx.x;
+    const int by = blockIdx.y;
+    bool need = false;
+    if (bx < g.mb_w) {
+        const size_t idx = (size_t)by * g.mb_w + bx;
+        const uint8_t m = a.map ? a.map[idx] : (uint8_t)1;
+        const size_t plane = (size_t)g.mb_w * g.mb_h;
+        need = (m | a.stale[(size_t)a.ring_idx * plane + idx]) != 0;
+        for (int j = 0; j < a.n_ring; j++) {
+            uint8_t *sp = a.stale + (size_t)j * plane + idx;
+            if (j == a.ring_idx) *sp = 0;
+            else if (m) *sp = 1;
+        }
+    }
+    if (need) {
+        const int y0 = by * 16;
+        const int rows = min(16, g.out_h - y0);              // out_h is even
+        const int wpx = min(16, g.out_w - bx * 16);          // valid pixels of this block (even)
+        // luma: `rows` segments of up to 16 bytes
+        const size_t yo = (size_t)y0 * g.y_stride + (size_t)bx * 16;
+        if (VEC && wpx == 16) {
+#pragma unroll 4
+            for (int r = 0; r < rows; r++)
+                *reinterpret_cast<uint4 *>(a.dst + yo + (size_t)r * g.y_stride) =
+                    *reinterpret_cast<const uint4 *>(a.src + yo + (size_t)r * g.y_stride);
+        } else {
+            const int nw = (wpx + 3) >> 2;                   // whole words; the row stride is a multiple of 4
+            for (int r = 0; r < rows; r++)
+                for (int k = 0; k < nw; k++)
+                    *reinterpret_cast<uint32_t *>(a.dst + yo + (size_t)r * g.y_stride + 4 * k) =
+                        *reinterpret_cast<const uint32_t *>(a.src + yo + (size_t)r * g.y_stride + 4 * k);
+        }
+        // chroma: rows/2 segments; NV12 = up to 16 interleaved bytes, I420 = up to 8 bytes in each plane
+        const int crow = rows >> 1;
+        if (FMT == 0) {
+            const size_t co = g.off_c0 + (size_t)(y0 >> 1) * g.c_stride + (size_t)bx * 16;
+            if (VEC && wpx == 16) {
+#pragma unroll 4
+                for (int r = 0; r < crow; r++)
+                    *reinterpret_cast<uint4 *>(a.dst + co + (size_t)r * g.c_stride) =
+                        *reinterpret_cast<const uint4 *>(a.src + co + (size_t)r * g.c_stride);
+            } else {
+                const int nw = (wpx + 3) >> 2;
+                for (int r = 0; r < crow; r++)
+                    for (int k = 0; k < nw; k++)
+                        *reinterpret_cast<uint32_t *>(a.dst + co + (size_t)r * g.c_stride + 4 * k) =
+                            *reinterpret_cast<const uint32_t *>(a.src + co + (size_t)r * g.c_stride + 4 * k);
+            }
+        } else {
+            const int nw = (wpx / 2 + 3) >> 2;
+            for (int pl = 0; pl < 2; pl++) {
+                const size_t co = (pl ? g.off_c1 : g.off_c0) + (size_t)(y0 >> 1) * g.c_stride + (size_t)bx * 8;
+                for (int r = 0; r < crow; r++)
+                    for (int k = 0; k < nw; k++)
+                        *reinterpret_cast<uint32_t *>(a.dst + co + (size_t)r * g.c_stride + 4 * k) =
+                            *reinterpret_cast<const uint32_t *>(a.src + co + (size_t)r * g.c_stride + 4 * k);
+            }
+        }
+    }
+    // number of macroblocks written, one RED per CTA
+    const int total = __syncthreads_count(need);
+    if (threadIdx.x == 0 && total != 0 && a.blocks_out != nullptr) atomicAdd(a.blocks_out, (uint32_t)total);
+}
+
 template <int RP, int QX, int HINT>
 cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
 {
@@ -1000,6 +1076,7 @@ cudaError_t launch_convert_shape(const SkGeom &g, const SkBatch &b, int n, cudaS
     return cudaErrorInvalidValue;
 }
 
+#ifdef SK_TUNING
 cudaError_t launch_convert_warp(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st)
 {
     const int tiles = ((g.out_w + 255) / 256) * ((g.out_h + 15) / 16);
@@ -1017,12 +1094,16 @@ cudaError_t launch_convert_warp(const SkGeom &g, const SkBatch &b, int n, cudaSt
 #undef SK_CASE
     return cudaErrorInvalidValue;
 }
+#endif  // SK_TUNING
 
 }  // namespace
 
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant)
 {
-    // variant 0 = library default, chosen by the sweep in profiles/ (RP=1, QX=2, plain __ldg)
+    // The release library carries ONE shape: RP=1, QX=2, plain 128-bit __ldg loads — the winner of the
+    // sweep in profiles/ (r1_default_ncu_summary.md).  The losing shapes and the cp.async.bulk (TMA engine)
+    // staging variant are compiled only into the tuning build (make tuning, -DSK_TUNING).
+#ifdef SK_TUNING
     switch (variant) {
     default:
     case 0: return launch_convert_shape<1, 2, 0>(g, b, n, st);
@@ -1042,6 +1123,10 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
     case 13: return launch_convert_shape<1, 2, 3>(g, b, n, st);   // default shape, streaming loads + stores
     case 14: return launch_convert_shape<1, 2, 4>(g, b, n, st);   // default shape, input rows staged by cp.async.bulk (TMA engine)
     }
+#else
+    (void)variant;
+    return launch_convert_shape<1, 2, 0>(g, b, n, st);
+#endif
 }
 
 cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int /*variant*/)
@@ -1082,4 +1167,34 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream
     SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
 #undef SK_CASE
     return cudaErrorInvalidValue;
+}
+
+cudaError_t sk_launch_gather(const SkGeom &g, const SkGather &a, cudaStream_t st)
+{
+    dim3 grid((g.mb_w + kThreads - 1) / kThreads, g.mb_h, 1);
+    dim3 block(kThreads);
+    // 16-byte stores need 16-byte aligned rows: every plane stride a multiple of 16 (all BASELINE widths)
+    const bool vec = (g.y_stride % 16 == 0) && (g.c_stride % 16 == 0) && (g.off_c0 % 16 == 0);
+    if (g.out_fmt == 0) {
+        if (vec) sk_gather_kernel<0, true><<<grid, block, 0, st>>>(g, a);
+        else sk_gather_kernel<0, false><<<grid, block, 0, st>>>(g, a);
+    } else {
+        if (g.y_stride % 16 == 0) sk_gather_kernel<1, true><<<grid, block, 0, st>>>(g, a);   // VEC: luma only
+        else sk_gather_kernel<1, false><<<grid, block, 0, st>>>(g, a);
+    }
+    return cudaGetLastError();
+}
+
+// Load every instantiation of the generic scale kernel into the current device's context now, so
+// that no later launch triggers a lazy module load (which allocates on the device).
+cudaError_t sk_preload_scale_generic()
+{
+    cudaFuncAttributes fa;
+    cudaError_t e;
+#define SK_CASE(FMT, SITE, DMG) \
+    if ((e = cudaFuncGetAttributes(&fa, sk_scale_kernel<FMT, SITE, DMG>)) != cudaSuccess) return e;
+    SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
+    SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
+#undef SK_CASE
+    return cudaSuccess;
 }

@@ -48,6 +48,18 @@ struct SkBatch {
     SkFrame f[SK_MAX_BATCH];
 };
 
+// Damage-gated read-back of one frame (sk_gather_kernel).
+struct SkGather {
+    const uint8_t *src;       // packed output frame in HBM
+    uint8_t *dst;             // persistent frame in mapped pinned host memory (device-visible address)
+    const uint8_t *map;       // this frame's damage map [mb_h][mb_w], or nullptr (copy everything)
+    uint8_t *stale;           // [n_ring][mb_h][mb_w]: blocks each host frame has missed so far
+    int n_ring, ring_idx;
+    uint32_t *blocks_out;     // += number of macroblocks written (zeroed on the stream by the caller)
+};
+cudaError_t sk_launch_gather(const SkGeom &g, const SkGather &a, cudaStream_t st);
+cudaError_t sk_preload_scale_generic();
+
 // variant: 0 = default. Returns the launch error (no sync).
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);
 cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);

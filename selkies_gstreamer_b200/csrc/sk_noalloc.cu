@@ -15,8 +15,9 @@
 //     cudaMalloc there can fail or fragment the pool, and the host's rule is simply
 //     "library code does not allocate".
 //
-// How.  It is the shrink+convert+damage kernel (sk_scale_kernel, which also handles
-// equal sizes) on caller-owned input/output buffers.  The kernel's scratch — the
+// How.  It is the generic shrink+convert+damage kernel (sk_scale_kernel: every output pixel gathers
+// its own taps; it also handles equal sizes — not the tiled kernel a session runs, which needs
+// per-session set-up) on caller-owned input/output buffers.  The kernel's scratch — the
 // reduction words of the damage count and the per-row vertical tap tables — lives in
 // one file-scope __device__ array of fixed size instead of cudaMalloc'd memory.  Every
 // GPU that loads the library carries that array (about 26 KB) until the process exits.
@@ -95,6 +96,8 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
     if (damage && (!d_map || !d_count)) return fail(errbuf, errbuf_len, SK_ERR_ARG, "d_map and d_count are required unless SK_FLAG_NO_DAMAGE is set");
     if (in_stride == 0) in_stride = (size_t)4 * in_w;
     if (in_stride < (size_t)4 * in_w) return fail(errbuf, errbuf_len, SK_ERR_ARG, "in_stride smaller than a row");
+    if ((uint64_t)in_stride * (uint64_t)in_h >= (1ull << 32))
+        return fail(errbuf, errbuf_len, SK_ERR_ARG, "in_stride * in_height must stay below 4 GiB (32-bit offsets in the kernel)");
     if (((uintptr_t)d_in & 3) || (in_stride & 3) || ((uintptr_t)d_out & 3) || ((uintptr_t)d_prev & 3) || ((uintptr_t)d_count & 3))
         return fail(errbuf, errbuf_len, SK_ERR_ALIGN, "d_in, in_stride, d_out, d_prev and d_count must be 4-byte aligned");
 
@@ -115,6 +118,10 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
         void *p = nullptr;
         if ((e = cudaGetSymbolAddress(&p, g_noalloc_scratch)) != cudaSuccess || !p)
             return fail(errbuf, errbuf_len, SK_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+        // ... and have every instantiation of the kernel loaded into this GPU's context now: a lazy
+        // code load on some later call (another format or chroma site) would allocate device memory.
+        if ((e = sk_preload_scale_generic()) != cudaSuccess)
+            return fail(errbuf, errbuf_len, SK_ERR_CUDA, "loading the scale kernels on device %d: %s", dev, cudaGetErrorString(e));
         pd.base = static_cast<unsigned char *>(p);
         pd.ready = true;
     }

@@ -23,14 +23,15 @@
 #include <string>
 #include <vector>
 
+static_assert(sizeof(sk_result) == 144 && sizeof(sk_config) == 72, "ABI structs changed: bump SK_ABI_VERSION and the bindings");
+
 namespace {
 
 constexpr int kMaxInflight = 8;
 constexpr size_t kCountHdr = 128;      // counts (one u32 per batch member) in front of the maps of a meta block
 std::atomic<uint64_t> g_launches{0};
-std::atomic<int> g_variant{0};
-std::atomic<int> g_snake{1};            // alternate traversal direction per launch (102 off / 103 on)
-std::atomic<int> g_scale_generic{0};   // tuning/testing: force the generic scale kernel
+std::atomic<int> g_variant{0};         // tuning build only (sk_tuning_set_variant); the release library has one shape
+std::atomic<int> g_snake{1};            // alternate traversal direction per launch (tuning build: 102 off / 103 on)
 thread_local std::string g_create_error;
 
 using skhost::ru;
@@ -53,11 +54,19 @@ struct Ring {          // one output ring entry (submission order)
     cudaEvent_t k_start = nullptr, k_done = nullptr;
     cudaEvent_t d2h_start = nullptr, done = nullptr;
     cudaEvent_t wait_on = nullptr;    // event sk_wait synchronises on (own `done` or a batch leader's)
+    cudaEvent_t kernel_done = nullptr; // event after the kernel that wrote d_out (own `k_done` or a batch leader's)
+    cudaEvent_t consumer_done = nullptr; // recorded by sk_release_device on the consumer's stream
+    bool consumer_pending = false;
     uint64_t frame_id = 0;
     bool valid = false;
     bool had_h2d = false;
     bool used = false;                // `done` has been recorded at least once
+    bool waited = false;              // the host has synchronised on wait_on since: nothing on the GPU still uses the entry
+    uint8_t *h_out_user = nullptr;    // caller's output buffer of this frame (sk_submit_io), else nullptr
+    uint8_t *h_out_dev = nullptr;     // device-visible address of h_out (mapped; gated read-back)
+    bool gated = false;               // this frame came back through the gather kernel
     const uint32_t *h_count = nullptr; // this frame's damaged-block count in pinned memory
+    const uint32_t *d_count = nullptr; // ... and where the kernel adds it up in HBM
 };
 
 }  // namespace
@@ -77,6 +86,8 @@ struct sk_session {
     Slot slots[kMaxInflight];
     Ring ring[kMaxInflight];
     uint32_t *d_state = nullptr;      // per-macroblock temporal policy state
+    uint8_t *d_stale = nullptr;       // gated read-back: [n][mb_h*mb_w] blocks each host frame has missed
+    bool bmeta_ready = false;         // leader: d_bmeta/h_bmeta allocated for every ring entry
     uint8_t *d_bmeta[kMaxInflight] = {};   // leader only: maps of all batch members, contiguous per ring entry
     uint8_t *h_bmeta[kMaxInflight] = {};
     int32_t *d_voff = nullptr;
@@ -88,6 +99,7 @@ struct sk_session {
     cudaStream_t last_kernel_stream = nullptr;
     cudaEvent_t last_kernel_event = nullptr;
     float last_kernel_us = 0.f;
+    uint32_t last_count = 0;
     std::string err;
 };
 
@@ -123,10 +135,11 @@ void free_session(sk_session *s)
         if (r.h_out) cudaFreeHost(r.h_out);
         if (r.d_meta) cudaFree(r.d_meta);
         if (r.h_meta) cudaFreeHost(r.h_meta);
-        cudaEvent_t evs[] = {r.h2d_start, r.h2d_done, r.k_start, r.k_done, r.d2h_start, r.done};
+        cudaEvent_t evs[] = {r.h2d_start, r.h2d_done, r.k_start, r.k_done, r.d2h_start, r.done, r.consumer_done};
         for (cudaEvent_t e : evs) if (e) cudaEventDestroy(e);
     }
     if (s->d_state) cudaFree(s->d_state);
+    if (s->d_stale) cudaFree(s->d_stale);
     for (int i = 0; i < kMaxInflight; i++) {
         if (s->d_bmeta[i]) cudaFree(s->d_bmeta[i]);
         if (s->h_bmeta[i]) cudaFreeHost(s->h_bmeta[i]);
@@ -146,6 +159,8 @@ int validate(const sk_config &c, std::string &why)
     if (bad_dim(c.in_width) || bad_dim(c.in_height)) { why = "input width/height must be even and in [2, 8192]"; return SK_ERR_ARG; }
     if (bad_dim(c.out_width) || bad_dim(c.out_height)) { why = "output width/height must be even and in [2, 8192]"; return SK_ERR_ARG; }
     if (c.in_stride < 4 * c.in_width) { why = "in_stride smaller than 4*in_width"; return SK_ERR_ARG; }
+    // the kernels address the input with 32-bit byte offsets
+    if ((uint64_t)ru(c.in_stride, 16) * (uint64_t)c.in_height >= (1ull << 32)) { why = "in_stride * in_height must stay below 4 GiB"; return SK_ERR_ARG; }
     if (c.in_format != SK_IN_BGRX && c.in_format != SK_IN_RGBX) { why = "unknown in_format"; return SK_ERR_ARG; }
     if (c.out_format != SK_OUT_NV12 && c.out_format != SK_OUT_I420) { why = "unknown out_format"; return SK_ERR_ARG; }
     if (c.matrix < SK_MATRIX_BT601 || c.matrix > SK_MATRIX_BT2020) { why = "unknown matrix"; return SK_ERR_ARG; }
@@ -154,6 +169,10 @@ int validate(const sk_config &c, std::string &why)
     auto bad_knob = [](int v) { return v < 1 || v > 255; };
     if (bad_knob(c.damage_block_threshold) || bad_knob(c.damage_block_duration) || bad_knob(c.paint_over_trigger_frames)) {
         why = "damage_block_threshold, damage_block_duration and paint_over_trigger_frames must be in [1, 255]";
+        return SK_ERR_ARG;
+    }
+    if ((c.flags & SK_FLAG_GATED_READBACK) && (!(c.flags & SK_FLAG_HOST_OUTPUT) || (c.flags & SK_FLAG_NO_DAMAGE))) {
+        why = "SK_FLAG_GATED_READBACK needs SK_FLAG_HOST_OUTPUT and the damage map";
         return SK_ERR_ARG;
     }
     const bool scaling = c.in_width != c.out_width || c.in_height != c.out_height;
@@ -187,6 +206,7 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     r.d_meta_view = r.d_meta + kCountHdr;
     r.h_meta_view = r.h_meta + kCountHdr;
     r.h_count = reinterpret_cast<const uint32_t *>(r.h_meta);
+    r.d_count = reinterpret_cast<const uint32_t *>(r.d_meta);
     f.map = r.d_meta_view;
     f.count_out = reinterpret_cast<uint32_t *>(r.d_meta);     // zeroed on the stream before the launch
     f.state = s->d_state;                       // nullptr unless SK_FLAG_POLICY
@@ -196,6 +216,9 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.v_tap = s->d_vtap;
     r.frame_id = frame_id;
     r.valid = true;
+    r.waited = false;
+    r.gated = false;
+    r.h_out_user = nullptr;
 
     s->prev_ring = ri;
     s->seq++;
@@ -211,45 +234,105 @@ cudaError_t launch(const sk_session *s, const SkGeom &g_in, const SkBatch &b, in
     return sk_launch_convert(g, b, n, st, g_variant.load());
 }
 
-// Everything after the kernel for one ring entry, on the session's own d2h stream.
-int enqueue_readback(sk_session *s, int ri, cudaEvent_t kernel_done)
+// What must have finished before `stream` may run the kernel that overwrites the ring entry `s`
+// will use next and reads the session's previous output.
+int wait_for_ring_entry(sk_session *err_to, sk_session *s, cudaStream_t stream, cudaEvent_t &already_waited)
 {
-    Ring &r = s->ring[ri];
-    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
-    const bool damage = !(s->cfg.flags & SK_FLAG_NO_DAMAGE);
-    const bool host_out = s->cfg.flags & SK_FLAG_HOST_OUTPUT;
-    SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, kernel_done, 0));
-    if (timing) SK_CUDA(s, cudaEventRecord(r.d2h_start, s->s_d2h));
-    if (damage)
-        SK_CUDA(s, cudaMemcpyAsync(r.h_meta, r.d_meta, kCountHdr + (s->d_state ? s->meta_bytes : s->map_bytes),
-                                   cudaMemcpyDeviceToHost, s->s_d2h));
-    if (host_out)
-        SK_CUDA(s, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
-    SK_CUDA(s, cudaEventRecord(r.done, s->s_d2h));
-    r.wait_on = r.done;
-    r.used = true;
+    Ring &r = s->ring[s->seq % (uint64_t)s->n];
+    // its read-back may still be running (unless the host has already waited for it)
+    if (r.used && !r.waited && r.wait_on != already_waited) {
+        SK_CUDA(err_to, cudaStreamWaitEvent(stream, r.wait_on, 0));
+        already_waited = r.wait_on;
+    }
+    // a device-side consumer may still be reading it (sk_release_device)
+    if (r.consumer_pending) {
+        SK_CUDA(err_to, cudaStreamWaitEvent(stream, r.consumer_done, 0));
+        r.consumer_pending = false;
+    }
+    // the session's previous kernel may have run on another stream (a batch leader's)
+    if (s->last_kernel_stream && s->last_kernel_stream != stream)
+        SK_CUDA(err_to, cudaStreamWaitEvent(stream, s->last_kernel_event, 0));
     return SK_OK;
 }
 
-int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot, uint64_t frame_id)
+// H2D of one captured frame into the device copy of `slot`, on the session's copy stream.
+// Pinned / registered memory is DMA'd asynchronously; pageable memory is staged by the driver before
+// the call returns.  Records the ring entry's h2d_done.
+int enqueue_h2d(sk_session *err_to, sk_session *s, int slot, const void *src, size_t stride)
+{
+    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
+    const size_t row = (size_t)4 * s->cfg.in_width;
+    Slot &sl = s->slots[slot];
+    Ring &r = s->ring[s->seq % (uint64_t)s->n];
+    // The device copy of this slot may still be read by an earlier kernel.
+    if (sl.consumed_valid) SK_CUDA(err_to, cudaStreamWaitEvent(s->s_copy, sl.consumed, 0));
+    if (timing) SK_CUDA(err_to, cudaEventRecord(r.h2d_start, s->s_copy));
+    if (stride == (size_t)s->d_in_stride) {
+        SK_CUDA(err_to, cudaMemcpyAsync(sl.d_in, src, stride * (size_t)(s->cfg.in_height - 1) + row,
+                                        cudaMemcpyHostToDevice, s->s_copy));
+    } else {
+        SK_CUDA(err_to, cudaMemcpy2DAsync(sl.d_in, s->d_in_stride, src, stride, row, s->cfg.in_height,
+                                          cudaMemcpyHostToDevice, s->s_copy));
+    }
+    SK_CUDA(err_to, cudaEventRecord(r.h2d_done, s->s_copy));
+    return SK_OK;
+}
+
+// Read-back of one ring entry on stream `st` (which already waits for the kernel): maps + counts,
+// then the frame — whole (copy engine) into the caller's buffer or the pinned ring, or only the
+// macroblocks that changed (gather kernel into the mapped persistent frame).
+int enqueue_frame_readback(sk_session *err_to, sk_session *s, int ri, cudaStream_t st, void *host_out, bool own_meta)
+{
+    Ring &r = s->ring[ri];
+    const bool damage = !(s->cfg.flags & SK_FLAG_NO_DAMAGE);
+    const bool host_out_flag = s->cfg.flags & SK_FLAG_HOST_OUTPUT;
+    r.h_out_user = static_cast<uint8_t *>(host_out);
+    if (s->d_stale && !host_out) {
+        SkGather a{};
+        a.src = r.d_out;
+        a.dst = r.h_out_dev;
+        a.map = r.d_meta_view;
+        a.stale = s->d_stale;
+        a.n_ring = s->n;
+        a.ring_idx = ri;
+        a.blocks_out = reinterpret_cast<uint32_t *>(r.d_meta) + 1;     // zeroed together with the count
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        SK_CUDA(err_to, sk_launch_gather(s->geom, a, st));
+        r.gated = true;
+    }
+    if (damage && own_meta)
+        SK_CUDA(err_to, cudaMemcpyAsync(r.h_meta, r.d_meta, kCountHdr + (s->d_state ? s->meta_bytes : s->map_bytes),
+                                        cudaMemcpyDeviceToHost, st));
+    if (host_out)
+        SK_CUDA(err_to, cudaMemcpyAsync(host_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, st));
+    else if (host_out_flag && !r.gated)
+        SK_CUDA(err_to, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, st));
+    return SK_OK;
+}
+
+int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot, uint64_t frame_id, void *host_out)
 {
     const bool timing = s->cfg.flags & SK_FLAG_TIMING;
     const int ri_next = (int)(s->seq % (uint64_t)s->n);
     Ring &r = s->ring[ri_next];
-    // The ring entry about to be overwritten may still be read by its D2H.
-    if (r.used) SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, r.wait_on, 0));
-    // A batch leader may have run this session's previous kernel on its stream.
-    if (s->last_kernel_stream && s->last_kernel_stream != s->s_comp)
-        SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, s->last_kernel_event, 0));
+    cudaEvent_t waited = nullptr;
+    int rc = wait_for_ring_entry(s, s, s->s_comp, waited);
+    if (rc != SK_OK) return rc;
     r.had_h2d = slot >= 0;
     if (slot >= 0) SK_CUDA(s, cudaStreamWaitEvent(s->s_comp, r.h2d_done, 0));
 
     SkBatch b;
     const int ri = stage_frame(s, d_in, frame_id, b.f[0]);
-    if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) SK_CUDA(s, cudaMemsetAsync(r.d_meta, 0, 4, s->s_comp));
+    if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) SK_CUDA(s, cudaMemsetAsync(r.d_meta, 0, 8, s->s_comp));
     if (timing) SK_CUDA(s, cudaEventRecord(r.k_start, s->s_comp));
-    SK_CUDA(s, launch(s, g, b, 1, s->s_comp));
+    cudaError_t le = launch(s, g, b, 1, s->s_comp);
+    if (le != cudaSuccess) {
+        s->prev_ring = -1;          // the ring entry was never written: the next frame has no predecessor
+        r.valid = false;
+        return fail(s, SK_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(le));
+    }
     SK_CUDA(s, cudaEventRecord(r.k_done, s->s_comp));
+    r.kernel_done = r.k_done;
     s->last_kernel_stream = s->s_comp;
     s->last_kernel_event = r.k_done;
     if (slot >= 0) {
@@ -257,7 +340,78 @@ int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot,
         SK_CUDA(s, cudaEventRecord(sl.consumed, s->s_comp));
         sl.consumed_valid = true;
     }
-    return enqueue_readback(s, ri, r.k_done);
+    SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, r.k_done, 0));
+    if (timing) SK_CUDA(s, cudaEventRecord(r.d2h_start, s->s_d2h));
+    rc = enqueue_frame_readback(s, s, ri, s->s_d2h, host_out, true);
+    if (rc != SK_OK) return rc;
+    SK_CUDA(s, cudaEventRecord(r.done, s->s_d2h));
+    r.wait_on = r.done;
+    r.used = true;
+    return SK_OK;
+}
+
+int check_slot(sk_session *s, int slot)
+{
+    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    return SK_OK;
+}
+
+// Members of one launch must agree on everything the kernel is specialised or parameterised on.
+int validate_batch(sk_session **ss, int n)
+{
+    sk_session *L = ss[0];
+    if (n > SK_MAX_BATCH) return fail(L, SK_ERR_ARG, "batch larger than SK_MAX_BATCH (32)");
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        if (!s) return fail(L, SK_ERR_ARG, "null session in batch");
+        const sk_config &a = L->cfg, &b = s->cfg;
+        if (s->dev != L->dev || a.in_width != b.in_width || a.in_height != b.in_height ||
+            a.out_width != b.out_width || a.out_height != b.out_height || a.in_format != b.in_format ||
+            a.out_format != b.out_format || a.matrix != b.matrix || a.chroma_site != b.chroma_site ||
+            a.scale_variant != b.scale_variant ||
+            ((a.flags ^ b.flags) & (SK_FLAG_NO_DAMAGE | SK_FLAG_POLICY | SK_FLAG_SCALE_GENERIC)) ||
+            a.damage_block_threshold != b.damage_block_threshold || a.damage_block_duration != b.damage_block_duration ||
+            a.paint_over_trigger_frames != b.paint_over_trigger_frames || a.n_inflight != b.n_inflight ||
+            s->d_in_stride != L->d_in_stride)
+            return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
+        if (s->cfg.flags & SK_FLAG_GATED_READBACK)
+            return fail(L, SK_ERR_UNSUPPORTED, "SK_FLAG_GATED_READBACK sessions cannot be batched");
+        for (int j = 0; j < i; j++)
+            if (ss[j] == s) return fail(L, SK_ERR_STATE, "a session appears twice in one batch");
+    }
+    return SK_OK;
+}
+
+// The leader's contiguous map blocks (one per ring entry), all or nothing.
+int prepare_bmeta(sk_session *L)
+{
+    if (L->bmeta_ready || (L->cfg.flags & SK_FLAG_NO_DAMAGE)) return SK_OK;
+    const size_t bytes = kCountHdr + (size_t)SK_MAX_BATCH * L->meta_bytes;
+    for (int k = 0; k < L->n; k++) {
+        cudaError_t e = cudaSuccess;
+        if (!L->d_bmeta[k]) e = cudaMalloc((void **)&L->d_bmeta[k], bytes);
+        if (e == cudaSuccess && !L->h_bmeta[k]) e = cudaHostAlloc((void **)&L->h_bmeta[k], bytes, cudaHostAllocDefault);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            for (int j = 0; j <= k; j++) {
+                if (L->d_bmeta[j]) { cudaFree(L->d_bmeta[j]); L->d_bmeta[j] = nullptr; }
+                if (L->h_bmeta[j]) { cudaFreeHost(L->h_bmeta[j]); L->h_bmeta[j] = nullptr; }
+            }
+            return fail(L, SK_ERR_NOMEM, std::string("batch map block: ") + cudaGetErrorString(e));
+        }
+    }
+    L->bmeta_ready = true;
+    return SK_OK;
+}
+
+// A batch step failed after some members' rings were advanced: their next frame has no predecessor.
+void abandon_batch(sk_session **ss, int n)
+{
+    for (int i = 0; i < n; i++) {
+        ss[i]->prev_ring = -1;
+        for (int k = 0; k < ss[i]->n; k++)
+            if (ss[i]->ring[k].valid && !ss[i]->ring[k].used) ss[i]->ring[k].valid = false;
+    }
 }
 
 }  // namespace
@@ -268,20 +422,19 @@ int sk_version(void) { return SK_ABI_VERSION; }
 
 uint64_t sk_launch_count(void) { return g_launches.load(); }
 
-int sk_set_kernel_variant(int variant)
+#ifdef SK_TUNING
+// Tuning build only (make tuning): process-wide kernel-shape selector for A/B runs; not in the public header.
+int sk_tuning_set_variant(int variant)
 {
     if (variant == 102 || variant == 103) {
         g_snake.store(variant == 103 ? 1 : 0);
-        return SK_OK;
-    }
-    if (variant == 100 || variant == 101) {     // 100: force the generic scale kernel for new sessions; 101: default
-        g_scale_generic.store(variant == 100 ? 1 : 0);
         return SK_OK;
     }
     if (variant < 0 || variant > 15) return SK_ERR_ARG;
     g_variant.store(variant);
     return SK_OK;
 }
+#endif
 
 int sk_device_count(void)
 {
@@ -357,11 +510,14 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     s->in_bytes_host = (size_t)c.in_stride * c.in_height;
     s->map_bytes = (size_t)ru(g.mb_w * g.mb_h, 4);
     s->meta_bytes = 2 * s->map_bytes;
+    const bool gated = c.flags & SK_FLAG_GATED_READBACK;
 
     SK_TRY(cudaStreamCreateWithFlags(&s->s_copy, cudaStreamNonBlocking));
     SK_TRY(cudaStreamCreateWithFlags(&s->s_comp, cudaStreamNonBlocking));
     SK_TRY(cudaStreamCreateWithFlags(&s->s_d2h, cudaStreamNonBlocking));
     const unsigned evflags = (c.flags & SK_FLAG_TIMING) ? cudaEventDefault : cudaEventDisableTiming;
+    // Events a host thread waits on put that thread to sleep instead of spinning, unless asked otherwise.
+    const unsigned waitflags = evflags | ((c.flags & SK_FLAG_SPIN_WAIT) ? 0u : (unsigned)cudaEventBlockingSync);
     for (int i = 0; i < s->n; i++) {
         Slot &sl = s->slots[i];
         SK_TRY(cudaHostAlloc((void **)&sl.h_in, s->in_bytes_host, cudaHostAllocDefault));
@@ -374,14 +530,26 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         SK_TRY(cudaMemset(r.d_meta, 0, kCountHdr + s->meta_bytes));
         SK_TRY(cudaHostAlloc((void **)&r.h_meta, kCountHdr + s->meta_bytes, cudaHostAllocDefault));
         std::memset(r.h_meta, 0, kCountHdr + s->meta_bytes);
-        if (c.flags & SK_FLAG_HOST_OUTPUT)
-            SK_TRY(cudaHostAlloc((void **)&r.h_out, s->frame_bytes, cudaHostAllocDefault));
-        cudaEvent_t *evs[] = {&r.h2d_start, &r.h2d_done, &r.k_start, &r.k_done, &r.d2h_start, &r.done};
+        if (c.flags & SK_FLAG_HOST_OUTPUT) {
+            SK_TRY(cudaHostAlloc((void **)&r.h_out, s->frame_bytes, gated ? cudaHostAllocMapped : cudaHostAllocDefault));
+            if (gated) {
+                std::memset(r.h_out, 0, s->frame_bytes);
+                SK_TRY(cudaHostGetDevicePointer((void **)&r.h_out_dev, r.h_out, 0));
+            }
+        }
+        cudaEvent_t *evs[] = {&r.h2d_start, &r.h2d_done, &r.k_start, &r.k_done, &r.d2h_start};
         for (cudaEvent_t *ev : evs) SK_TRY(cudaEventCreateWithFlags(ev, evflags));
+        SK_TRY(cudaEventCreateWithFlags(&r.done, waitflags));
+        SK_TRY(cudaEventCreateWithFlags(&r.consumer_done, cudaEventDisableTiming));
     }
     if ((c.flags & SK_FLAG_POLICY) && !(c.flags & SK_FLAG_NO_DAMAGE)) {
         SK_TRY(cudaMalloc((void **)&s->d_state, s->map_bytes * sizeof(uint32_t)));
         SK_TRY(cudaMemset(s->d_state, 0, s->map_bytes * sizeof(uint32_t)));
+    }
+    if (gated) {
+        // every host frame starts out missing every block
+        SK_TRY(cudaMalloc((void **)&s->d_stale, (size_t)s->n * g.mb_w * g.mb_h));
+        SK_TRY(cudaMemset(s->d_stale, 1, (size_t)s->n * g.mb_w * g.mb_h));
     }
     for (cudaEvent_t &ev : s->mark) SK_TRY(cudaEventCreate(&ev));
     if (s->scaling) {
@@ -421,7 +589,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
         g.scale_fast = (order_ok && max_rows <= 40 && max_chunks <= 96 && smem <= 96 * 1024 &&
-                        g_scale_generic.load() == 0) ? 1 : 0;
+                        !(c.flags & SK_FLAG_SCALE_GENERIC)) ? 1 : 0;
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -443,7 +611,7 @@ int sk_session_destroy(sk_session *s)
 int sk_get_input_staging(sk_session *s, int slot, void **host_ptr, size_t *bytes)
 {
     if (!s || !host_ptr) return SK_ERR_ARG;
-    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    if (check_slot(s, slot) != SK_OK) return SK_ERR_ARG;
     *host_ptr = s->slots[slot].h_in;
     if (bytes) *bytes = s->in_bytes_host;
     return SK_OK;
@@ -452,7 +620,7 @@ int sk_get_input_staging(sk_session *s, int slot, void **host_ptr, size_t *bytes
 int sk_get_device_input(sk_session *s, int slot, void **dptr, size_t *stride)
 {
     if (!s || !dptr) return SK_ERR_ARG;
-    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    if (check_slot(s, slot) != SK_OK) return SK_ERR_ARG;
     *dptr = s->slots[slot].d_in;
     if (stride) *stride = (size_t)s->d_in_stride;
     return SK_OK;
@@ -461,7 +629,7 @@ int sk_get_device_input(sk_session *s, int slot, void **dptr, size_t *stride)
 int sk_upload(sk_session *s, int slot, const void *src, size_t src_stride)
 {
     if (!s || !src) return SK_ERR_ARG;
-    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    if (check_slot(s, slot) != SK_OK) return SK_ERR_ARG;
     const size_t row = (size_t)4 * s->cfg.in_width;
     if (src_stride == 0) src_stride = row;
     if (src_stride < row) return fail(s, SK_ERR_ARG, "src_stride smaller than a row");
@@ -478,50 +646,33 @@ int sk_upload(sk_session *s, int slot, const void *src, size_t src_stride)
 int sk_submit(sk_session *s, int slot, uint64_t frame_id)
 {
     if (!s) return SK_ERR_ARG;
-    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
+    if (check_slot(s, slot) != SK_OK) return SK_ERR_ARG;
     SK_CUDA(s, cudaSetDevice(s->dev));
-    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
-    Slot &sl = s->slots[slot];
-    Ring &r = s->ring[s->seq % (uint64_t)s->n];
-    // The device copy of this slot may still be read by an earlier kernel.
-    if (sl.consumed_valid) SK_CUDA(s, cudaStreamWaitEvent(s->s_copy, sl.consumed, 0));
-    if (timing) SK_CUDA(s, cudaEventRecord(r.h2d_start, s->s_copy));
-    if (s->d_in_stride == s->cfg.in_stride) {
-        SK_CUDA(s, cudaMemcpyAsync(sl.d_in, sl.h_in, s->in_bytes_host, cudaMemcpyHostToDevice, s->s_copy));
-    } else {
-        SK_CUDA(s, cudaMemcpy2DAsync(sl.d_in, s->d_in_stride, sl.h_in, s->cfg.in_stride,
-                                     (size_t)4 * s->cfg.in_width, s->cfg.in_height,
-                                     cudaMemcpyHostToDevice, s->s_copy));
-    }
-    SK_CUDA(s, cudaEventRecord(r.h2d_done, s->s_copy));
-    return submit_common(s, s->geom, sl.d_in, slot, frame_id);
+    int rc = enqueue_h2d(s, s, slot, s->slots[slot].h_in, (size_t)s->cfg.in_stride);
+    if (rc != SK_OK) return rc;
+    return submit_common(s, s->geom, s->slots[slot].d_in, slot, frame_id, nullptr);
+}
+
+int sk_submit_io(sk_session *s, int slot, const void *host_in, size_t in_stride, void *host_out, uint64_t frame_id)
+{
+    if (!s || !host_in) return SK_ERR_ARG;
+    if (check_slot(s, slot) != SK_OK) return SK_ERR_ARG;
+    const size_t row = (size_t)4 * s->cfg.in_width;
+    if (in_stride == 0) in_stride = row;
+    if (in_stride < row) return fail(s, SK_ERR_ARG, "stride smaller than a row");
+    if (host_out && s->d_stale)
+        return fail(s, SK_ERR_UNSUPPORTED, "a SK_FLAG_GATED_READBACK session keeps its own persistent host frames: host_out must be NULL");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    // Straight from the caller's buffer into the device slot: no trip through the pinned staging.
+    // Either way the buffer must stay valid until sk_wait(frame_id) returns.
+    int rc = enqueue_h2d(s, s, slot, host_in, in_stride);
+    if (rc != SK_OK) return rc;
+    return submit_common(s, s->geom, s->slots[slot].d_in, slot, frame_id, host_out);
 }
 
 int sk_submit_host(sk_session *s, int slot, const void *host_ptr, size_t stride, uint64_t frame_id)
 {
-    if (!s || !host_ptr) return SK_ERR_ARG;
-    if (slot < 0 || slot >= s->n) return fail(s, SK_ERR_ARG, "slot out of range");
-    const size_t row = (size_t)4 * s->cfg.in_width;
-    if (stride == 0) stride = row;
-    if (stride < row) return fail(s, SK_ERR_ARG, "stride smaller than a row");
-    SK_CUDA(s, cudaSetDevice(s->dev));
-    const bool timing = s->cfg.flags & SK_FLAG_TIMING;
-    Slot &sl = s->slots[slot];
-    Ring &r = s->ring[s->seq % (uint64_t)s->n];
-    if (sl.consumed_valid) SK_CUDA(s, cudaStreamWaitEvent(s->s_copy, sl.consumed, 0));
-    if (timing) SK_CUDA(s, cudaEventRecord(r.h2d_start, s->s_copy));
-    // Straight from the caller's buffer into the device slot: no trip through the pinned staging.
-    // Pinned / registered memory is DMA'd asynchronously; pageable memory is staged by the driver
-    // before this returns.  Either way the buffer must stay valid until sk_wait(frame_id) returns.
-    if (stride == (size_t)s->d_in_stride) {
-        SK_CUDA(s, cudaMemcpyAsync(sl.d_in, host_ptr, stride * (size_t)(s->cfg.in_height - 1) + row,
-                                   cudaMemcpyHostToDevice, s->s_copy));
-    } else {
-        SK_CUDA(s, cudaMemcpy2DAsync(sl.d_in, s->d_in_stride, host_ptr, stride, row, s->cfg.in_height,
-                                     cudaMemcpyHostToDevice, s->s_copy));
-    }
-    SK_CUDA(s, cudaEventRecord(r.h2d_done, s->s_copy));
-    return submit_common(s, s->geom, sl.d_in, slot, frame_id);
+    return sk_submit_io(s, slot, host_ptr, stride, nullptr, frame_id);
 }
 
 int sk_host_register(void *ptr, size_t bytes)
@@ -552,10 +703,20 @@ int sk_submit_device(sk_session *s, const void *dptr, size_t stride, uint64_t fr
     if (stride == 0) stride = (size_t)s->d_in_stride;
     if (((uintptr_t)dptr & 15) || (stride & 15)) return fail(s, SK_ERR_ALIGN, "device frame pointer and stride must be 16-byte aligned");
     if (stride < (size_t)4 * s->cfg.in_width) return fail(s, SK_ERR_ARG, "stride smaller than a row");
+    if ((uint64_t)stride * (uint64_t)s->cfg.in_height >= (1ull << 32)) return fail(s, SK_ERR_ARG, "stride * in_height must stay below 4 GiB");
     SK_CUDA(s, cudaSetDevice(s->dev));
     SkGeom g = s->geom;
     g.in_stride = (int)stride;
-    return submit_common(s, g, (const uint8_t *)dptr, -1, frame_id);
+    return submit_common(s, g, (const uint8_t *)dptr, -1, frame_id, nullptr);
+}
+
+int sk_batch_prepare(sk_session **ss, int n)
+{
+    if (!ss || n < 1 || !ss[0]) return SK_ERR_ARG;
+    int rc = validate_batch(ss, n);
+    if (rc != SK_OK) return rc;
+    SK_CUDA(ss[0], cudaSetDevice(ss[0]->dev));
+    return prepare_bmeta(ss[0]);
 }
 
 int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t stride, uint64_t frame_id)
@@ -563,26 +724,22 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
     if (!ss || !dptrs || n < 1) return SK_ERR_ARG;
     sk_session *L = ss[0];
     if (!L) return SK_ERR_ARG;
-    if (n > SK_MAX_BATCH) return fail(L, SK_ERR_ARG, "batch larger than SK_MAX_BATCH (32)");
+    // ---- everything that can be refused or has to be allocated comes before any ring is advanced
+    int rc = validate_batch(ss, n);
+    if (rc != SK_OK) return rc;
     if (stride == 0) stride = (size_t)L->d_in_stride;
     if (stride & 15) return fail(L, SK_ERR_ALIGN, "stride must be 16-byte aligned");
+    if (stride < (size_t)4 * L->cfg.in_width) return fail(L, SK_ERR_ARG, "stride smaller than a row");
+    if ((uint64_t)stride * (uint64_t)L->cfg.in_height >= (1ull << 32)) return fail(L, SK_ERR_ARG, "stride * in_height must stay below 4 GiB");
     for (int i = 0; i < n; i++) {
-        sk_session *s = ss[i];
-        if (!s || !dptrs[i]) return fail(L, SK_ERR_ARG, "null session or frame in batch");
+        if (!dptrs[i]) return fail(L, SK_ERR_ARG, "null frame in batch");
         if ((uintptr_t)dptrs[i] & 15) return fail(L, SK_ERR_ALIGN, "device frame pointers must be 16-byte aligned");
-        const sk_config &a = L->cfg, &b = s->cfg;
-        if (s->dev != L->dev || a.in_width != b.in_width || a.in_height != b.in_height ||
-            a.out_width != b.out_width || a.out_height != b.out_height || a.in_format != b.in_format ||
-            a.out_format != b.out_format || a.matrix != b.matrix || a.chroma_site != b.chroma_site ||
-            a.scale_variant != b.scale_variant || ((a.flags ^ b.flags) & (SK_FLAG_NO_DAMAGE | SK_FLAG_POLICY)) ||
-            a.damage_block_threshold != b.damage_block_threshold || a.damage_block_duration != b.damage_block_duration ||
-            a.paint_over_trigger_frames != b.paint_over_trigger_frames || a.n_inflight != b.n_inflight)
-            return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
-        for (int j = 0; j < i; j++)
-            if (ss[j] == s) return fail(L, SK_ERR_STATE, "a session appears twice in one batch");
     }
     SK_CUDA(L, cudaSetDevice(L->dev));
+    if ((rc = prepare_bmeta(L)) != SK_OK) return rc;     // no-op after sk_batch_prepare / the first batch
+
     const bool timing = L->cfg.flags & SK_FLAG_TIMING;
+    const bool damage = !(L->cfg.flags & SK_FLAG_NO_DAMAGE);
     SkGeom g = L->geom;
     g.in_stride = (int)stride;
     SkBatch b;
@@ -590,63 +747,157 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
     cudaEvent_t waited = nullptr;      // members of a steady batch share one event: wait on it once
     for (int i = 0; i < n; i++) {
         sk_session *s = ss[i];
-        Ring &r = s->ring[s->seq % (uint64_t)s->n];
-        if (r.used && r.wait_on != waited) {
-            SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, r.wait_on, 0));
-            waited = r.wait_on;
-        }
-        if (s->last_kernel_stream && s->last_kernel_stream != L->s_comp)
-            SK_CUDA(L, cudaStreamWaitEvent(L->s_comp, s->last_kernel_event, 0));
-        r.had_h2d = false;
+        if ((rc = wait_for_ring_entry(L, s, L->s_comp, waited)) != SK_OK) { abandon_batch(ss, i); return rc; }
+        s->ring[s->seq % (uint64_t)s->n].had_h2d = false;
         ris[i] = stage_frame(s, (const uint8_t *)dptrs[i], frame_id, b.f[i]);
     }
-    Ring &lr = L->ring[ris[0]];
-    const bool damage = !(L->cfg.flags & SK_FLAG_NO_DAMAGE);
+    const int lri = ris[0];
+    Ring &lr = L->ring[lri];
     if (damage) {
-        // All members' maps land in one block owned by the leader (allocated at the first batch), so the
-        // read-back is ONE copy per step instead of one small copy per session.
-        const int lri = ris[0];
-        if (!L->d_bmeta[lri]) {
-            SK_CUDA(L, cudaMalloc((void **)&L->d_bmeta[lri], kCountHdr + (size_t)SK_MAX_BATCH * L->meta_bytes));
-            SK_CUDA(L, cudaHostAlloc((void **)&L->h_bmeta[lri], kCountHdr + (size_t)SK_MAX_BATCH * L->meta_bytes, cudaHostAllocDefault));
-        }
+        // All members' maps land in one block owned by the leader, so the read-back is ONE copy per
+        // step instead of one small copy per session.
         for (int i = 0; i < n; i++) {
             Ring &r = ss[i]->ring[ris[i]];
             r.d_meta_view = L->d_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
             r.h_meta_view = L->h_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
             r.h_count = reinterpret_cast<const uint32_t *>(L->h_bmeta[lri]) + i;
+            r.d_count = reinterpret_cast<const uint32_t *>(L->d_bmeta[lri]) + i;
             b.f[i].count_out = reinterpret_cast<uint32_t *>(L->d_bmeta[lri]) + i;
             b.f[i].map = r.d_meta_view;
             b.f[i].policy = r.d_meta_view + L->map_bytes;
         }
     }
-    if (damage) SK_CUDA(L, cudaMemsetAsync(L->d_bmeta[ris[0]], 0, kCountHdr, L->s_comp));
-    if (timing) SK_CUDA(L, cudaEventRecord(lr.k_start, L->s_comp));
-    SK_CUDA(L, launch(L, g, b, n, L->s_comp));
-    SK_CUDA(L, cudaEventRecord(lr.k_done, L->s_comp));
+#define SK_BATCH_CUDA(call)                                                                          \
+    do {                                                                                             \
+        cudaError_t e_ = (call);                                                                     \
+        if (e_ != cudaSuccess) {                                                                     \
+            abandon_batch(ss, n);                                                                    \
+            return fail(L, SK_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
+        }                                                                                            \
+    } while (0)
+    if (damage) SK_BATCH_CUDA(cudaMemsetAsync(L->d_bmeta[lri], 0, kCountHdr, L->s_comp));
+    if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
+    SK_BATCH_CUDA(launch(L, g, b, n, L->s_comp));
+    SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
     // Read-back of every member rides on the leader's d2h stream; one event closes the batch.
-    SK_CUDA(L, cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
-    if (timing) SK_CUDA(L, cudaEventRecord(lr.d2h_start, L->s_d2h));
+    SK_BATCH_CUDA(cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
+    if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.d2h_start, L->s_d2h));
     if (damage)
-        SK_CUDA(L, cudaMemcpyAsync(L->h_bmeta[ris[0]], L->d_bmeta[ris[0]], kCountHdr + (size_t)n * L->meta_bytes,
-                                   cudaMemcpyDeviceToHost, L->s_d2h));
+        SK_BATCH_CUDA(cudaMemcpyAsync(L->h_bmeta[lri], L->d_bmeta[lri], kCountHdr + (size_t)n * L->meta_bytes,
+                                      cudaMemcpyDeviceToHost, L->s_d2h));
     for (int i = 0; i < n; i++) {
-        sk_session *s = ss[i];
-        Ring &r = s->ring[ris[i]];
-        if (s->cfg.flags & SK_FLAG_HOST_OUTPUT)
-            SK_CUDA(L, cudaMemcpyAsync(r.h_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, L->s_d2h));
+        if ((rc = enqueue_frame_readback(L, ss[i], ris[i], L->s_d2h, nullptr, false)) != SK_OK) { abandon_batch(ss, n); return rc; }
     }
-    SK_CUDA(L, cudaEventRecord(lr.done, L->s_d2h));
+    SK_BATCH_CUDA(cudaEventRecord(lr.done, L->s_d2h));
     for (int i = 0; i < n; i++) {
         sk_session *s = ss[i];
         Ring &r = s->ring[ris[i]];
         r.wait_on = lr.done;
+        r.kernel_done = lr.k_done;
         r.used = true;
         s->last_kernel_stream = L->s_comp;
         s->last_kernel_event = lr.k_done;
     }
     return SK_OK;
 }
+
+int sk_batch_submit_host(sk_session **ss, int n, const void *const *host_in, size_t in_stride,
+                         void *const *host_out, uint64_t frame_id)
+{
+    if (!ss || !host_in || n < 1) return SK_ERR_ARG;
+    sk_session *L = ss[0];
+    if (!L) return SK_ERR_ARG;
+    int rc = validate_batch(ss, n);
+    if (rc != SK_OK) return rc;
+    const size_t row = (size_t)4 * L->cfg.in_width;
+    if (in_stride == 0) in_stride = row;
+    if (in_stride < row) return fail(L, SK_ERR_ARG, "stride smaller than a row");
+    for (int i = 0; i < n; i++)
+        if (!host_in[i]) return fail(L, SK_ERR_ARG, "null frame in batch");
+    SK_CUDA(L, cudaSetDevice(L->dev));
+
+    const bool timing = L->cfg.flags & SK_FLAG_TIMING;
+    const bool damage = !(L->cfg.flags & SK_FLAG_NO_DAMAGE);
+    SkBatch b;
+    int ris[SK_MAX_BATCH];
+    int slots[SK_MAX_BATCH];
+    cudaEvent_t waited = nullptr;
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        // each member's frame goes up on its own copy stream, into the device slot that pairs with
+        // the ring entry it is about to fill; the leader's compute stream waits for every upload
+        slots[i] = (int)(s->seq % (uint64_t)s->n);
+        Ring &r = s->ring[slots[i]];
+        if ((rc = enqueue_h2d(L, s, slots[i], host_in[i], in_stride)) != SK_OK) { abandon_batch(ss, i); return rc; }
+        if ((rc = wait_for_ring_entry(L, s, L->s_comp, waited)) != SK_OK) { abandon_batch(ss, i); return rc; }
+        cudaError_t e = cudaStreamWaitEvent(L->s_comp, r.h2d_done, 0);
+        if (e != cudaSuccess) { abandon_batch(ss, i); return fail(L, SK_ERR_CUDA, std::string("cudaStreamWaitEvent: ") + cudaGetErrorString(e)); }
+        r.had_h2d = true;
+        ris[i] = stage_frame(s, s->slots[slots[i]].d_in, frame_id, b.f[i]);
+    }
+    Ring &lr = L->ring[ris[0]];
+    if (damage)
+        for (int i = 0; i < n; i++)
+            SK_BATCH_CUDA(cudaMemsetAsync(ss[i]->ring[ris[i]].d_meta, 0, 8, L->s_comp));
+    if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
+    SK_BATCH_CUDA(launch(L, L->geom, b, n, L->s_comp));
+    SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
+    for (int i = 0; i < n; i++) {
+        Slot &sl = ss[i]->slots[slots[i]];
+        SK_BATCH_CUDA(cudaEventRecord(sl.consumed, L->s_comp));
+        sl.consumed_valid = true;
+    }
+    SK_BATCH_CUDA(cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
+    if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.d2h_start, L->s_d2h));
+    for (int i = 0; i < n; i++) {
+        void *ho = host_out ? host_out[i] : nullptr;
+        if ((rc = enqueue_frame_readback(L, ss[i], ris[i], L->s_d2h, ho, true)) != SK_OK) { abandon_batch(ss, n); return rc; }
+    }
+    SK_BATCH_CUDA(cudaEventRecord(lr.done, L->s_d2h));
+#undef SK_BATCH_CUDA
+    for (int i = 0; i < n; i++) {
+        sk_session *s = ss[i];
+        Ring &r = s->ring[ris[i]];
+        r.wait_on = lr.done;
+        r.kernel_done = lr.k_done;
+        r.used = true;
+        s->last_kernel_stream = L->s_comp;
+        s->last_kernel_event = lr.k_done;
+    }
+    return SK_OK;
+}
+
+namespace {
+void describe(sk_session *s, Ring &r, uint64_t frame_id, sk_result *out, bool host_side)
+{
+    std::memset(out, 0, sizeof(*out));
+    out->frame_id = frame_id;
+    out->dev_frame = r.d_out;
+    out->frame_bytes = s->frame_bytes;
+    for (int i = 0; i < 3; i++) {
+        out->plane_offset[i] = s->plane_offset[i];
+        out->plane_stride[i] = s->plane_stride[i];
+    }
+    out->mb_w = s->geom.mb_w;
+    out->mb_h = s->geom.mb_h;
+    const bool damage = !(s->cfg.flags & SK_FLAG_NO_DAMAGE);
+    if (damage) {
+        out->dev_damage_map = r.d_meta_view;
+        out->dev_damaged_count = r.d_count;
+        if (s->d_state) out->dev_policy_map = r.d_meta_view + s->map_bytes;
+    }
+    if (!host_side) return;
+    if (r.h_out_user) out->host_frame = r.h_out_user;
+    else if (s->cfg.flags & SK_FLAG_HOST_OUTPUT) out->host_frame = r.h_out;
+    if (out->host_frame)
+        out->readback_bytes = r.gated ? (uint64_t)reinterpret_cast<const uint32_t *>(r.h_meta)[1] * 384u : s->frame_bytes;
+    if (damage) {
+        out->host_damage_map = r.h_meta_view;
+        out->damaged_count = *r.h_count;
+        if (s->d_state) out->host_policy_map = r.h_meta_view + s->map_bytes;
+    }
+}
+}  // namespace
 
 int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
 {
@@ -656,6 +907,10 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
     Ring &r = s->ring[ri];
     SK_CUDA(s, cudaSetDevice(s->dev));
     SK_CUDA(s, cudaEventSynchronize(r.wait_on));
+    // The host has seen this frame complete: later submissions need not chain on its events again (a
+    // batch leader that owned them may even be gone by then).
+    r.waited = true;
+    if (s->last_kernel_event == r.kernel_done) s->last_kernel_stream = nullptr;
     const bool timing = s->cfg.flags & SK_FLAG_TIMING;
     const bool own_events = r.wait_on == r.done;
     if (timing && own_events) {
@@ -664,26 +919,7 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
         else cudaGetLastError();
     }
     if (out) {
-        std::memset(out, 0, sizeof(*out));
-        out->frame_id = frame_id;
-        out->dev_frame = r.d_out;
-        out->host_frame = (s->cfg.flags & SK_FLAG_HOST_OUTPUT) ? r.h_out : nullptr;
-        out->frame_bytes = s->frame_bytes;
-        for (int i = 0; i < 3; i++) {
-            out->plane_offset[i] = s->plane_offset[i];
-            out->plane_stride[i] = s->plane_stride[i];
-        }
-        out->mb_w = s->geom.mb_w;
-        out->mb_h = s->geom.mb_h;
-        if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) {
-            out->host_damage_map = r.h_meta_view;
-            out->dev_damage_map = r.d_meta_view;
-            out->damaged_count = *r.h_count;
-            if (s->d_state) {
-                out->host_policy_map = r.h_meta_view + s->map_bytes;
-                out->dev_policy_map = r.d_meta_view + s->map_bytes;
-            }
-        }
+        describe(s, r, frame_id, out, true);
         if (timing && own_events) {
             float ms = 0.f;
             out->kernel_us = s->last_kernel_us;
@@ -692,6 +928,45 @@ int sk_wait(sk_session *s, uint64_t frame_id, sk_result *out)
             cudaGetLastError();
         }
     }
+    return SK_OK;
+}
+
+int sk_read_frame(sk_session *s, uint64_t frame_id, void *host_out)
+{
+    if (!s || !host_out) return SK_ERR_ARG;
+    const int ri = find_ring(s, frame_id);
+    if (ri < 0) return fail(s, SK_ERR_STATE, "unknown frame id (never submitted, or its ring entry was reused)");
+    Ring &r = s->ring[ri];
+    if (!r.kernel_done) return fail(s, SK_ERR_STATE, "frame has no kernel queued");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaStreamWaitEvent(s->s_d2h, r.kernel_done, 0));
+    SK_CUDA(s, cudaMemcpyAsync(host_out, r.d_out, s->frame_bytes, cudaMemcpyDeviceToHost, s->s_d2h));
+    SK_CUDA(s, cudaStreamSynchronize(s->s_d2h));
+    return SK_OK;
+}
+
+int sk_wait_device(sk_session *s, uint64_t frame_id, void *cuda_stream, sk_result *out)
+{
+    if (!s) return SK_ERR_ARG;
+    const int ri = find_ring(s, frame_id);
+    if (ri < 0) return fail(s, SK_ERR_STATE, "unknown frame id (never submitted, or its ring entry was reused)");
+    Ring &r = s->ring[ri];
+    if (!r.kernel_done) return fail(s, SK_ERR_STATE, "frame has no kernel queued");
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaStreamWaitEvent((cudaStream_t)cuda_stream, r.kernel_done, 0));
+    if (out) describe(s, r, frame_id, out, false);
+    return SK_OK;
+}
+
+int sk_release_device(sk_session *s, uint64_t frame_id, void *cuda_stream)
+{
+    if (!s) return SK_ERR_ARG;
+    const int ri = find_ring(s, frame_id);
+    if (ri < 0) return fail(s, SK_ERR_STATE, "unknown frame id (never submitted, or its ring entry was reused)");
+    Ring &r = s->ring[ri];
+    SK_CUDA(s, cudaSetDevice(s->dev));
+    SK_CUDA(s, cudaEventRecord(r.consumer_done, (cudaStream_t)cuda_stream));
+    r.consumer_pending = true;
     return SK_OK;
 }
 
@@ -724,6 +999,8 @@ int sk_batch_wait(sk_session **ss, int n, uint64_t frame_id, uint32_t *damaged_c
             damaged_counts[i] = res.damaged_count;
             continue;
         }
+        r.waited = true;
+        if (s->last_kernel_event == r.kernel_done) s->last_kernel_stream = nullptr;
         damaged_counts[i] = *r.h_count;
     }
     return SK_OK;
@@ -753,6 +1030,61 @@ int sk_marker_elapsed_us(sk_session *s, float *us)
     float ms = 0.f;
     SK_CUDA(s, cudaEventElapsedTime(&ms, s->mark[0], s->mark[1]));
     *us = ms * 1e3f;
+    return SK_OK;
+}
+
+int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_gbs, double *d2h_gbs)
+{
+    if (bytes == 0 || iters < 1 || mode < 0 || mode > 2) return SK_ERR_ARG;
+    if (h2d_gbs) *h2d_gbs = 0.0;
+    if (d2h_gbs) *d2h_gbs = 0.0;
+    if (device_id < 0) device_id = 0;
+    void *h[2] = {nullptr, nullptr}, *d[2] = {nullptr, nullptr};
+    cudaStream_t st[2] = {nullptr, nullptr};
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaError_t e = cudaSetDevice(device_id);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+        e = cudaHostAlloc(&h[i], bytes, cudaHostAllocDefault);
+        if (e == cudaSuccess) { std::memset(h[i], 0x5a, bytes); e = cudaMalloc(&d[i], bytes); }
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&ev[2 * i]);
+        if (e == cudaSuccess) e = cudaEventCreate(&ev[2 * i + 1]);
+    }
+    const bool up = mode != 1, down = mode != 0;
+    if (e == cudaSuccess) {
+        // one untimed pass each way, then the timed loops (both started before either is waited for)
+        if (up) e = cudaMemcpyAsync(d[0], h[0], bytes, cudaMemcpyHostToDevice, st[0]);
+        if (e == cudaSuccess && down) e = cudaMemcpyAsync(h[1], d[1], bytes, cudaMemcpyDeviceToHost, st[1]);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    }
+    if (e == cudaSuccess) {
+        if (up) cudaEventRecord(ev[0], st[0]);
+        if (down) cudaEventRecord(ev[2], st[1]);
+        for (int k = 0; k < iters && e == cudaSuccess; k++) {
+            if (up) e = cudaMemcpyAsync(d[0], h[0], bytes, cudaMemcpyHostToDevice, st[0]);
+            if (e == cudaSuccess && down) e = cudaMemcpyAsync(h[1], d[1], bytes, cudaMemcpyDeviceToHost, st[1]);
+        }
+        if (up) cudaEventRecord(ev[1], st[0]);
+        if (down) cudaEventRecord(ev[3], st[1]);
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    }
+    if (e == cudaSuccess) {
+        float ms = 0.f;
+        if (up && cudaEventElapsedTime(&ms, ev[0], ev[1]) == cudaSuccess && ms > 0.f && h2d_gbs)
+            *h2d_gbs = (double)bytes * iters / (ms * 1e-3) / 1e9;
+        if (down && cudaEventElapsedTime(&ms, ev[2], ev[3]) == cudaSuccess && ms > 0.f && d2h_gbs)
+            *d2h_gbs = (double)bytes * iters / (ms * 1e-3) / 1e9;
+    }
+    for (int i = 0; i < 2; i++) {
+        if (h[i]) cudaFreeHost(h[i]);
+        if (d[i]) cudaFree(d[i]);
+        if (st[i]) cudaStreamDestroy(st[i]);
+    }
+    for (cudaEvent_t v : ev) if (v) cudaEventDestroy(v);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(nullptr, SK_ERR_CUDA, std::string("sk_pcie_probe: ") + cudaGetErrorString(e));
+    }
     return SK_OK;
 }
 

@@ -65,11 +65,13 @@ class _mapped:
         if lib is not None:
             self._info = _GstMapInfo()
             flags = 2 if self.write else 1            # GST_MAP_WRITE / GST_MAP_READ
-            if not lib.gst_buffer_map(hash(self.buf), ctypes.byref(self._info), flags):
-                self._info = None
-                raise _MapError("gst_buffer_map failed")
-            self.ptr, self.size = self._info.data, self._info.size
-            return self
+            if lib.gst_buffer_map(hash(self.buf), ctypes.byref(self._info), flags):
+                self.ptr, self.size = self._info.data, self._info.size
+                return self
+            # e.g. a WRITE map refused because PyGObject holds an extra reference on outbuf inside
+            # do_transform (the buffer is then not "writable"): take the copying path below instead
+            # of failing the frame.
+            self._info = None
         if self.write:
             self.size = self.buf.get_size()
             self._tmp = (ctypes.c_uint8 * self.size)()
@@ -159,10 +161,21 @@ def element_class():
             "keyframe-damage-fraction": (GObject.TYPE_DOUBLE, "keyframe-damage-fraction",
                                          "damaged fraction of the frame that requests a key unit", 0.0, 1.0, 0.6,
                                          GObject.ParamFlags.READWRITE),
+            "min-keyframe-distance": (GObject.TYPE_UINT, "min-keyframe-distance",
+                                      "fewest frames between two key-unit requests (cf. the reference's "
+                                      "min_keyframe_frame_distance, gstwebrtc_app.py:1227-1262)",
+                                      0, GObject.G_MAXUINT, 60, GObject.ParamFlags.READWRITE),
+            "pin-buffers": (GObject.TYPE_BOOLEAN, "pin-buffers", "page-lock the pool buffers the element is handed, so "
+                            "both PCIe copies are DMA (turn off if upstream/downstream do not use buffer pools)", True,
+                            GObject.ParamFlags.READWRITE),
+            "coalesce": (GObject.TYPE_BOOLEAN, "coalesce", "share kernel launches with the other b200preencode "
+                         "elements of this process that have the same caps and GPU", False, GObject.ParamFlags.READWRITE),
             "roi-meta": (GObject.TYPE_BOOLEAN, "roi-meta", "attach GstVideoRegionOfInterestMeta for damaged / "
                          "paint-over regions (x264enc honours them)", True, GObject.ParamFlags.READWRITE),
             "force-keyframes": (GObject.TYPE_BOOLEAN, "force-keyframes", "send downstream force-key-unit when the "
-                                "damaged fraction crosses keyframe-damage-fraction", True, GObject.ParamFlags.READWRITE),
+                                "damaged fraction RISES above keyframe-damage-fraction (never more often than "
+                                "min-keyframe-distance; steady damage is left to the encoder's rate control)", True,
+                                GObject.ParamFlags.READWRITE),
             "paint-over-delta-qp": (GObject.TYPE_INT, "paint-over-delta-qp", "delta-qp put on paint-over regions",
                                     -51, 51, -8, GObject.ParamFlags.READWRITE),
             "damaged-blocks": (GObject.TYPE_UINT, "damaged-blocks", "damaged macroblocks in the last frame",

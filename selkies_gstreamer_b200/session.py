@@ -54,6 +54,10 @@ class FrameResult:
     kernel_us: float
     d2h_us: float
     policy_map: np.ndarray | None = None   # uint8 [mb_h, mb_w] of SK_POLICY_* bits
+    dev_policy_map: int = 0
+    dev_damaged_count: int = 0      # device address of the uint32 count
+    readback_bytes: int = 0         # frame bytes that crossed PCIe for `frame`
+    host_frame_ptr: int = 0         # address of the host copy (library ring, or the caller's buffer of submit_io)
 
 
 class PreencodeSession:
@@ -62,7 +66,8 @@ class PreencodeSession:
                  colorimetry=None, chroma_site=None, device_id: int = -1, n_inflight: int = 2,
                  in_stride: int = 0, damage: bool = True, host_output: bool = True, timing: bool = False,
                  scale_variant: int = _abi.SK_SCALE_VARIANT_GST_LQ, policy: bool = False, damage_block_threshold: int = 0,
-                 damage_block_duration: int = 0, paint_over_trigger_frames: int = 0):
+                 damage_block_duration: int = 0, paint_over_trigger_frames: int = 0, scale_generic: bool = False,
+                 spin_wait: bool = False, gated_readback: bool = False):
         self._lib = _abi.load()
         self._h = ctypes.c_void_p()
         if in_format.upper() not in IN_FORMATS:
@@ -77,8 +82,14 @@ class PreencodeSession:
         self.in_stride = int(in_stride) or 4 * self.width
         self.n_inflight = n_inflight
         flags = (0 if damage else _abi.SK_FLAG_NO_DAMAGE) | (_abi.SK_FLAG_HOST_OUTPUT if host_output else 0) \
-            | (_abi.SK_FLAG_TIMING if timing else 0) | (_abi.SK_FLAG_POLICY if policy else 0)
+            | (_abi.SK_FLAG_TIMING if timing else 0) | (_abi.SK_FLAG_POLICY if policy else 0) \
+            | (_abi.SK_FLAG_SCALE_GENERIC if scale_generic else 0) | (_abi.SK_FLAG_SPIN_WAIT if spin_wait else 0) \
+            | (_abi.SK_FLAG_GATED_READBACK if gated_readback else 0)
         self.flags = flags
+        self.device_index = max(0, int(device_id))
+        self.scale_variant = int(scale_variant)
+        self.policy_knobs = (int(damage_block_threshold) or 10, int(damage_block_duration) or 20,
+                             int(paint_over_trigger_frames) or 15)
         cfg = _abi.SkConfig(ctypes.sizeof(_abi.SkConfig), device_id, self.width, self.height, self.in_stride,
                             IN_FORMATS[in_format.upper()], self.out_width, self.out_height,
                             OUT_FORMATS[self.out_format], self.matrix, self.site, _abi.SK_SCALE_BILINEAR,
@@ -156,6 +167,14 @@ class PreencodeSession:
         self._check(self._lib.sk_submit_host(self._h, slot, ctypes.c_void_p(ptr), stride, fid))
         return fid
 
+    def submit_io(self, slot: int, in_ptr: int, in_stride: int, out_ptr: int | None, frame_id: int | None = None) -> int:
+        """sk_submit_io: H2D straight from the caller's input buffer and the converted frame copied back into
+        the caller's output buffer (both raw addresses; pin recycled buffers with host_register)."""
+        fid = self._take_id(frame_id)
+        self._check(self._lib.sk_submit_io(self._h, slot, ctypes.c_void_p(in_ptr), in_stride,
+                                           ctypes.c_void_p(out_ptr) if out_ptr else None, fid))
+        return fid
+
     def submit_device(self, dptr: int, stride: int = 0, frame_id: int | None = None) -> int:
         fid = self._take_id(frame_id)
         self._check(self._lib.sk_submit_device(self._h, ctypes.c_void_p(dptr), stride, fid))
@@ -167,25 +186,49 @@ class PreencodeSession:
         self._next_id = int(frame_id) + 1
         return int(frame_id)
 
-    def wait(self, frame_id: int) -> FrameResult:
-        """Block until `frame_id` is done. `frame` and `damage_map` are BORROWED views of the
-        library's pinned buffers: valid until n_inflight more frames are submitted or the
-        session is closed — copy them if they must outlive that."""
-        r = _abi.SkResult()
-        self._check(self._lib.sk_wait(self._h, frame_id, ctypes.byref(r)))
-        frame = dmap = None
+    def _result(self, r) -> FrameResult:
+        frame = dmap = pmap = None
         if r.host_frame:
             buf = (ctypes.c_uint8 * r.frame_bytes).from_address(r.host_frame)
             frame = np.frombuffer(buf, dtype=np.uint8)
         if r.host_damage_map:
             buf = (ctypes.c_uint8 * (r.mb_w * r.mb_h)).from_address(r.host_damage_map)
             dmap = np.frombuffer(buf, dtype=np.uint8).reshape(r.mb_h, r.mb_w)
-        pmap = None
         if r.host_policy_map:
             buf = (ctypes.c_uint8 * (r.mb_w * r.mb_h)).from_address(r.host_policy_map)
             pmap = np.frombuffer(buf, dtype=np.uint8).reshape(r.mb_h, r.mb_w)
         return FrameResult(r.frame_id, frame, dmap, r.damaged_count, r.dev_frame or 0, r.dev_damage_map or 0,
-                           tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us, pmap)
+                           tuple(r.plane_offset), tuple(r.plane_stride), r.h2d_us, r.kernel_us, r.d2h_us, pmap,
+                           r.dev_policy_map or 0, r.dev_damaged_count or 0, int(r.readback_bytes), r.host_frame or 0)
+
+    def wait(self, frame_id: int) -> FrameResult:
+        """Block until `frame_id` is done. `frame` and `damage_map` are BORROWED views of the
+        library's pinned buffers (or of the caller's output buffer): valid until n_inflight more
+        frames are submitted or the session is closed — copy them if they must outlive that."""
+        r = _abi.SkResult()
+        self._check(self._lib.sk_wait(self._h, frame_id, ctypes.byref(r)))
+        return self._result(r)
+
+    def read_frame(self, frame_id: int, out: np.ndarray | None = None) -> np.ndarray:
+        """sk_read_frame: blocking copy of the converted frame of `frame_id` out of HBM."""
+        if out is None:
+            out = np.empty(self.frame_bytes, np.uint8)
+        if out.dtype != np.uint8 or out.nbytes < self.frame_bytes or not out.flags.c_contiguous:
+            raise ValueError("need a contiguous uint8 buffer of frame_bytes")
+        self._check(self._lib.sk_read_frame(self._h, frame_id, ctypes.c_void_p(out.ctypes.data)))
+        return out
+
+    def wait_device(self, frame_id: int, cuda_stream: int) -> FrameResult:
+        """sk_wait_device: make `cuda_stream` (a cudaStream_t as an integer) wait for the kernel of
+        `frame_id`; returns at once with the device pointers only."""
+        r = _abi.SkResult()
+        self._check(self._lib.sk_wait_device(self._h, frame_id, ctypes.c_void_p(cuda_stream), ctypes.byref(r)))
+        return self._result(r)
+
+    def release_device(self, frame_id: int, cuda_stream: int):
+        """sk_release_device: the ring entry of `frame_id` is not overwritten before the work queued on
+        `cuda_stream` so far has finished."""
+        self._check(self._lib.sk_release_device(self._h, frame_id, ctypes.c_void_p(cuda_stream)))
 
     def convert(self, frame: np.ndarray, slot: int = 0, copy: bool = False) -> FrameResult:
         """Synchronous convenience: upload → submit → wait (see wait() about borrowed views)."""
@@ -271,6 +314,23 @@ class SessionBatch:
             raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
         return frame_id
 
+    def prepare(self):
+        """sk_batch_prepare: allocate the leader's map blocks now, not at the first submit."""
+        rc = self._lib.sk_batch_prepare(self._handles, self._n)
+        if rc != _abi.SK_OK:
+            raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
+
+    def submit_host(self, in_ptrs: list[int], in_stride: int, out_ptrs: list[int] | None, frame_id: int) -> int:
+        """sk_batch_submit_host: frames still in host memory, one upload per member, ONE launch."""
+        ins = (ctypes.c_void_p * self._n)(*in_ptrs)
+        outs = (ctypes.c_void_p * self._n)(*out_ptrs) if out_ptrs is not None else None
+        rc = self._lib.sk_batch_submit_host(self._handles, self._n, ins, in_stride, outs, frame_id)
+        if rc != _abi.SK_OK:
+            raise PreencodeError(rc, (self._lib.sk_last_error(self.sessions[0]._h) or b"").decode())
+        for s in self.sessions:
+            s._next_id = frame_id + 1
+        return frame_id
+
     def wait(self, frame_id: int) -> list[int]:
         rc = self._lib.sk_batch_wait(self._handles, self._n, frame_id, self._counts)
         if rc != _abi.SK_OK:
@@ -278,17 +338,20 @@ class SessionBatch:
         return list(self._counts)
 
 
-def host_register(array: np.ndarray):
-    """Pin a caller-owned numpy buffer (a capture segment) for submit_host. Undo with host_unregister."""
+def host_register(array, nbytes: int | None = None):
+    """Pin a caller-owned buffer (numpy array, or raw address + nbytes: a capture segment, a pool
+    buffer) for submit_host / submit_io. Undo with host_unregister."""
     lib = _abi.load()
-    rc = lib.sk_host_register(ctypes.c_void_p(array.ctypes.data), array.nbytes)
+    ptr, n = (array.ctypes.data, array.nbytes) if isinstance(array, np.ndarray) else (int(array), int(nbytes))
+    rc = lib.sk_host_register(ctypes.c_void_p(ptr), n)
     if rc != _abi.SK_OK:
         raise PreencodeError(rc, (lib.sk_last_error(None) or b"").decode())
 
 
-def host_unregister(array: np.ndarray):
+def host_unregister(array):
     lib = _abi.load()
-    rc = lib.sk_host_unregister(ctypes.c_void_p(array.ctypes.data))
+    ptr = array.ctypes.data if isinstance(array, np.ndarray) else int(array)
+    rc = lib.sk_host_unregister(ctypes.c_void_p(ptr))
     if rc != _abi.SK_OK:
         raise PreencodeError(rc, (lib.sk_last_error(None) or b"").decode())
 

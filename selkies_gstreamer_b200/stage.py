@@ -25,7 +25,9 @@ import threading
 from fractions import Fraction
 
 from . import _abi, colorimetry as _col
+from .coalesce import LaunchCoalescer
 from .damage_policy import DamagePolicy
+from .hostbuf import PinCache
 from .session import PreencodeError, PreencodeSession, frame_layout
 
 SINK_FORMATS = ("BGRx", "BGRA", "RGBx", "RGBA")
@@ -214,13 +216,25 @@ class PreEncodeStage:
         "damage-block-duration": (int, 20, lambda v: 1 <= v <= 255),
         "paint-over-trigger-frames": (int, 15, lambda v: 1 <= v <= 255),
         "keyframe-damage-fraction": (float, 0.6, lambda v: 0.0 < v <= 1.0),
+        "min-keyframe-distance": (int, 60, lambda v: v >= 0),        # frames; cf. min_keyframe_frame_distance (gstwebrtc_app.py:1227-1262)
+        # host side of the frame path
+        "pin-buffers": (bool, True, None),           # page-lock the (recycled) buffers transform() is handed: DMA both ways
+        "pin-cache-size": (int, 16, lambda v: 0 <= v <= 256),
+        "coalesce": (bool, False, None),             # share launches with the other stages of this process (coalesce.py)
+        "coalesce-window-us": (int, 200, lambda v: 0 <= v <= 100000),
+        "spin-wait": (bool, False, None),            # busy-poll for completion instead of sleeping
     }
     READ_ONLY = ("frames", "damaged-blocks", "damaged-fraction", "total-blocks")
 
     def __init__(self, name: str = "b200preencode0"):
         self.name = name
         self._props = {k: d for k, (_, d, _) in self.PROPERTIES.items()}
-        self._lock = threading.Lock()       # set_caps may come from another thread than transform (§8b)
+        # set_caps / set_property may come from another thread than transform (§8b).  transform() holds the
+        # lock only to submit; while it sleeps on the GPU the session is kept alive by `_busy`.
+        self._lock = threading.Condition()
+        self._busy = 0
+        self._pins = PinCache(16)
+        self._coalescer: LaunchCoalescer | None = None
         self._session: PreencodeSession | None = None
         self._in = self._out = None
         self._started = False
@@ -261,10 +275,16 @@ class PreEncodeStage:
         with self._lock:
             changed = self._props[name] != value
             self._props[name] = value
-            needs_session = name in ("cuda-device-id", "damage", "n-inflight", "scale-variant",
-                                     "damage-block-threshold", "damage-block-duration", "paint-over-trigger-frames")
+            needs_session = name in ("cuda-device-id", "damage", "n-inflight", "scale-variant", "spin-wait", "coalesce",
+                                     "coalesce-window-us", "damage-block-threshold", "damage-block-duration",
+                                     "paint-over-trigger-frames")
             if name == "keyframe-damage-fraction" and self._policy is not None:
                 self._policy.keyframe_fraction = value
+            if name == "min-keyframe-distance" and self._policy is not None:
+                self._policy.min_keyframe_distance = value
+            if name in ("pin-buffers", "pin-cache-size") and changed:
+                self._pins.release()
+                self._pins = PinCache(self._props["pin-cache-size"] if self._props["pin-buffers"] else 0)
             if changed and needs_session and self._session is not None:
                 self._recreate_locked()
 
@@ -357,11 +377,20 @@ class PreEncodeStage:
 
     def stop(self) -> bool:
         with self._lock:
-            if self._session is not None:
-                self._session.close()
-                self._session = None
+            self._close_session_locked()
+            self._pins.release()
             self._started = False
         return True
+
+    def _close_session_locked(self):
+        """Destroy the GPU session once no transform() is sleeping on it."""
+        self._lock.wait_for(lambda: self._busy == 0)
+        if self._session is not None:
+            if self._coalescer is not None:
+                self._coalescer.detach(self._session)
+                self._coalescer = None
+            self._session.close()
+            self._session = None
 
     def set_caps(self, incaps: dict, outcaps: dict) -> bool:
         """(Re)create the GPU session for fixed caps; the next frame has no predecessor."""
@@ -390,20 +419,26 @@ class PreEncodeStage:
             return False
 
     def _recreate_locked(self):
-        if self._session is not None:
-            self._session.close()
-            self._session = None
+        self._close_session_locked()
+        self._pins.release()            # new caps, new buffer pools
         i, o = self._in, self._out
+        # The frame comes back into the buffer transform() is given (sk_submit_io), so the session
+        # keeps no pinned output ring of its own.
         self._session = PreencodeSession(
             i["width"], i["height"], in_format=i["format"], out_format=o["format"],
             out_width=o["width"], out_height=o["height"], colorimetry=o.get("colorimetry"),
             chroma_site=o.get("chroma-site"), device_id=self._props["cuda-device-id"],
-            n_inflight=self._props["n-inflight"], damage=self._props["damage"], host_output=True,
+            n_inflight=self._props["n-inflight"], damage=self._props["damage"], host_output=False,
             scale_variant=self._props["scale-variant"], policy=self._props["damage"],
             damage_block_threshold=self._props["damage-block-threshold"],
             damage_block_duration=self._props["damage-block-duration"],
-            paint_over_trigger_frames=self._props["paint-over-trigger-frames"])
-        self._policy = DamagePolicy(o["width"], o["height"], self._props["keyframe-damage-fraction"])
+            paint_over_trigger_frames=self._props["paint-over-trigger-frames"],
+            spin_wait=self._props["spin-wait"])
+        if self._props["coalesce"]:
+            self._coalescer = LaunchCoalescer.for_session(self._session, self._props["coalesce-window-us"])
+            self._coalescer.attach()
+        self._policy = DamagePolicy(o["width"], o["height"], self._props["keyframe-damage-fraction"],
+                                    self._props["min-keyframe-distance"])
         self.frames = 0
 
     @property
@@ -416,8 +451,14 @@ class PreEncodeStage:
         return {} if s is None else {"colorimetry": _col.MATRIX_NAMES[s.matrix], "chroma-site": _col.SITE_NAMES[s.site]}
 
     # -- per frame --------------------------------------------------------------
-    def transform(self, in_ptr: int, in_size: int, out_ptr: int, out_size: int, in_stride: int = 0) -> int:
-        """One frame: raw host pointers in, raw host pointers out. Returns a FlowReturn value."""
+    def transform(self, in_ptr: int, in_size: int, out_ptr: int, out_size: int, in_stride: int = 0,
+                  pin: bool | None = None) -> int:
+        """One frame: raw host pointers in, raw host pointers out. Returns a FlowReturn value.
+
+        H2D straight from the input buffer, D2H straight into the output buffer — no host-side copy.
+        Buffers that come round again (buffer pools) are page-locked on first sight (`pin-buffers`;
+        `pin=False` for one-off buffers: a pinned buffer must stay mapped until the stage stops or
+        renegotiates, as pool memory does)."""
         with self._lock:
             s = self._session
             if s is None:
@@ -425,29 +466,45 @@ class PreEncodeStage:
                 return FLOW_NOT_NEGOTIATED
             try:
                 stride = in_stride or 4 * s.width
-                if in_size < stride * (s.height - 1) + 4 * s.width:
+                need_in = stride * (s.height - 1) + 4 * s.width
+                if in_size < need_in:
                     raise StageError(f"input buffer too small: {in_size} bytes")
                 if out_size < s.frame_bytes:
                     raise StageError(f"output buffer too small: {out_size} < {s.frame_bytes}")
-                slot = self.frames % s.n_inflight
-                # H2D straight from the mapped input buffer; it stays mapped until wait() returns
-                r = s.wait(s.submit_host(slot, in_ptr, stride))
-                ctypes.memmove(out_ptr, r.frame.ctypes.data, s.frame_bytes)
-                self.frames += 1
-                # copies: the session's pinned buffers are reused n_inflight frames later
-                self.last_damage_map = None if r.damage_map is None else r.damage_map.copy()
-                self.last_policy_map = None if r.policy_map is None else r.policy_map.copy()
-                self.last_damaged = r.damaged_count
-                if r.damage_map is not None:
-                    if self.on_damage is not None:
-                        self.on_damage(self, self.last_damage_map, r.damaged_count)
-                    self.last_decision = self._policy.decide(self.last_damage_map, self.last_policy_map, r.damaged_count)
-                    if self.on_decision is not None:
-                        self.on_decision(self, self.last_decision)
-                return FLOW_OK
+                if self._props["pin-buffers"] if pin is None else pin:
+                    self._pins.ensure(in_ptr, in_size)
+                    self._pins.ensure(out_ptr, out_size)
+                co = self._coalescer if stride == s.in_stride else None
+                fid = None
+                if co is None:
+                    # both buffers stay mapped until wait() returns
+                    fid = s.submit_io(self.frames % s.n_inflight, in_ptr, stride, out_ptr)
+                self._busy += 1
             except (StageError, PreencodeError) as e:
                 self.last_error = str(e)
                 return FLOW_ERROR
+        # The GPU works; this thread sleeps without holding the lock (properties stay settable).
+        try:
+            r = co.convert(s, in_ptr, stride, out_ptr) if co is not None else s.wait(fid)
+            self.frames += 1
+            # copies: the session's pinned map buffers are reused n_inflight frames later
+            self.last_damage_map = None if r.damage_map is None else r.damage_map.copy()
+            self.last_policy_map = None if r.policy_map is None else r.policy_map.copy()
+            self.last_damaged = r.damaged_count
+            if r.damage_map is not None:
+                if self.on_damage is not None:
+                    self.on_damage(self, self.last_damage_map, r.damaged_count)
+                self.last_decision = self._policy.decide(self.last_damage_map, self.last_policy_map, r.damaged_count)
+                if self.on_decision is not None:
+                    self.on_decision(self, self.last_decision)
+            return FLOW_OK
+        except (StageError, PreencodeError) as e:
+            self.last_error = str(e)
+            return FLOW_ERROR
+        finally:
+            with self._lock:
+                self._busy -= 1
+                self._lock.notify_all()
 
     def transform_array(self, frame):
         """numpy convenience around transform(): returns (packed output, damage map, count)."""
@@ -457,7 +514,7 @@ class PreEncodeStage:
             raise StageError("not negotiated")
         frame = np.ascontiguousarray(frame)
         out = np.empty(s.frame_bytes, np.uint8)
-        rc = self.transform(frame.ctypes.data, frame.nbytes, out.ctypes.data, out.nbytes)
+        rc = self.transform(frame.ctypes.data, frame.nbytes, out.ctypes.data, out.nbytes, pin=False)
         if rc != FLOW_OK:
             raise StageError(self.last_error)
         return out, (None if self.last_damage_map is None else self.last_damage_map.copy()), self.last_damaged

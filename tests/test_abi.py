@@ -37,8 +37,9 @@ def test_library_exports_every_declared_symbol(lib):
 def test_version_and_struct_sizes(lib):
     assert lib.sk_version() == _abi.SK_ABI_VERSION
     assert ctypes.sizeof(_abi.SkConfig) == 18 * 4
-    # the header's sk_result: u64, 2 ptr, size_t, 3 size_t, 3 i32 (+pad), 2 ptr, 2 i32, u32, 3 float
-    assert ctypes.sizeof(_abi.SkResult) == 8 + 16 + 8 + 24 + 16 + 16 + 8 + 4 + 12 + 16
+    # the header's sk_result: u64, 2 ptr, size_t, 3 size_t, 3 i32 (+pad), 2 ptr, 2 i32, u32, 3 float, 2 ptr, ptr, u64
+    # (the library static_asserts the same number)
+    assert ctypes.sizeof(_abi.SkResult) == 8 + 16 + 8 + 24 + 16 + 16 + 8 + 4 + 12 + 16 + 8 + 8 == 144
 
 
 def test_header_cites_reference_lines():
@@ -63,6 +64,9 @@ def test_bad_struct_size_is_rejected(lib):
     (dict(chroma_site=3), _abi.SK_ERR_ARG),
     (dict(n_inflight=1), _abi.SK_ERR_ARG),
     (dict(in_stride=100), _abi.SK_ERR_ARG),
+    (dict(in_width=2, in_height=8192, in_stride=1 << 20), _abi.SK_ERR_ARG),   # 32-bit byte offsets in the kernels
+    (dict(flags=_abi.SK_FLAG_GATED_READBACK), _abi.SK_ERR_ARG),              # needs SK_FLAG_HOST_OUTPUT
+    (dict(flags=_abi.SK_FLAG_GATED_READBACK | _abi.SK_FLAG_HOST_OUTPUT | _abi.SK_FLAG_NO_DAMAGE), _abi.SK_ERR_ARG),
     (dict(out_width=3840, out_height=2160), _abi.SK_ERR_UNSUPPORTED),   # enlarging
     (dict(damage_block_threshold=300), _abi.SK_ERR_ARG),
     (dict(paint_over_trigger_frames=-1), _abi.SK_ERR_ARG),
@@ -109,3 +113,17 @@ def test_null_handles_are_rejected(lib):
     assert lib.sk_submit(None, 0, 0) == _abi.SK_ERR_ARG
     assert lib.sk_wait(None, 0, None) == _abi.SK_ERR_ARG
     assert lib.sk_reset_history(None) == _abi.SK_ERR_ARG
+    assert lib.sk_submit_io(None, 0, None, 0, None, 0) == _abi.SK_ERR_ARG
+    assert lib.sk_wait_device(None, 0, None, None) == _abi.SK_ERR_ARG
+    assert lib.sk_release_device(None, 0, None) == _abi.SK_ERR_ARG
+    assert lib.sk_read_frame(None, 0, None) == _abi.SK_ERR_ARG
+    assert lib.sk_batch_prepare(None, 0) == _abi.SK_ERR_ARG
+    assert lib.sk_batch_submit_host(None, 0, None, 0, None, 0) == _abi.SK_ERR_ARG
+    assert lib.sk_pcie_probe(0, 0, 1, 0, None, None) == _abi.SK_ERR_ARG
+
+
+def test_release_library_has_no_tuning_selector(lib):
+    """The process-wide kernel-shape switch of the round-1 sweep lives in the tuning build only."""
+    assert not hasattr(lib, "sk_set_kernel_variant")
+    if "tuning" not in os.path.basename(_abi.LIB_PATH):
+        assert not hasattr(lib, "sk_tuning_set_variant")

@@ -1,5 +1,5 @@
-"""Multi-GPU host logic on CPU: session→GPU placement and the world_size-2 gloo
-reduction bench.py uses (no data-path collective exists to test)."""
+"""Multi-GPU host logic on CPU: bench.py's session→GPU placement and its world_size-2 gloo
+reductions (no data-path collective exists to test: sessions share nothing)."""
 import os
 import socket
 import subprocess
@@ -8,7 +8,7 @@ import textwrap
 
 import pytest
 
-from selkies_gstreamer_b200 import sharding
+import bench as sharding
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -42,12 +42,14 @@ def test_world_size_2_gloo_max_over_ranks(tmp_path):
         import os, sys
         sys.path.insert(0, {ROOT!r})
         import torch.distributed as dist
-        from selkies_gstreamer_b200 import sharding
+        import bench as sharding
         rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
         dist.init_process_group("gloo", rank=rank, world_size=world)
         mine = sharding.sessions_of_rank(rank, world, 5)
         dist.barrier()
-        t = sharding.reduce_max_time(dist, 1.0 + rank)          # rank 1 is the slow one
+        t = sharding.reduce_over_ranks(dist, [1.0 + rank], "max")[0]          # rank 1 is the slow one
+        assert sharding.reduce_over_ranks(dist, [1.0], "sum")[0] == world
+        assert sharding.reduce_over_ranks(None, [3.5], "min") == [3.5]
         frames = [len(sharding.sessions_of_rank(r, world, 5)) * 10 for r in range(world)]
         fps = sharding.aggregate_fps(frames, [t] * world)
         dist.barrier()

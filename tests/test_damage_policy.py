@@ -132,7 +132,7 @@ def test_too_many_regions_fall_back_to_row_band_boxes():
 
 
 def test_decisions():
-    pol = DamagePolicy(640, 360, keyframe_fraction=0.5)
+    pol = DamagePolicy(640, 360, keyframe_fraction=0.5, min_keyframe_distance=0)
     mbh, mbw = 23, 40
     ones = np.ones((mbh, mbw), np.uint8)
     zeros = np.zeros((mbh, mbw), np.uint8)
@@ -153,3 +153,26 @@ def test_decisions():
     assert pol.decide(zeros, None).force_keyframe        # first frame after a reset
     with pytest.raises(ValueError):
         DamagePolicy(64, 64, keyframe_fraction=0.0)
+
+
+def test_keyframes_only_on_the_rising_edge_and_not_too_often():
+    """Full-screen video / games / scrolling damage every frame: the reference runs an infinite GOP
+    under a tight VBV (gstwebrtc_app.py:1227-1262), so steady damage must not turn every frame into an IDR."""
+    mbh, mbw = 23, 40
+    ones = np.ones((mbh, mbw), np.uint8)
+    zeros = np.zeros((mbh, mbw), np.uint8)
+    pol = DamagePolicy(640, 360, keyframe_fraction=0.6, min_keyframe_distance=30)
+    forced = [pol.decide(ones, None).force_keyframe for _ in range(100)]
+    assert forced[0] and sum(forced) == 1                  # only the implicit first frame
+    # still for a moment, then a scene change: one request on the rising edge ...
+    pol.decide(zeros, None)
+    seq = [pol.decide(ones, None).force_keyframe for _ in range(5)]
+    assert seq == [True, False, False, False, False]
+    # ... but a second flip right after is too soon (min distance 30 frames)
+    pol.decide(zeros, None)
+    assert not pol.decide(ones, None).force_keyframe
+    for _ in range(30):
+        pol.decide(zeros, None)
+    assert pol.decide(ones, None).force_keyframe
+    with pytest.raises(ValueError):
+        DamagePolicy(64, 64, min_keyframe_distance=-1)

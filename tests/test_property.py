@@ -54,8 +54,10 @@ def test_gpu_convert_random_geometry(w, h, m, site, fmt, infmt, variant, seed):
         f1[y, x, :3] ^= 0x5A
     ofmt, oin = {"NV12": 0, "I420": 1}[fmt], {"BGRx": 0, "RGBx": 1}[infmt]
     lib = _abi.load()
+    tuning = hasattr(lib, "sk_tuning_set_variant")      # the release library has the default shape only
     try:
-        lib.sk_set_kernel_variant(variant)
+        if tuning:
+            lib.sk_tuning_set_variant(variant)
         with PreencodeSession(w, h, in_format=infmt, out_format=fmt, colorimetry=m, chroma_site=site) as s:
             prev = None
             for i, f in enumerate((f0, f1, f1)):
@@ -66,7 +68,8 @@ def test_gpu_convert_random_geometry(w, h, m, site, fmt, infmt, variant, seed):
                 assert (r.damage_map == em).all() and r.damaged_count == en
                 prev = e
     finally:
-        lib.sk_set_kernel_variant(0)
+        if tuning:
+            lib.sk_tuning_set_variant(0)
 
 
 @pytest.mark.gpu
@@ -81,18 +84,13 @@ def test_gpu_scale_random_geometry(w, h, fx, fy, var, site, fmt, generic, seed):
     f1 = f0.copy()
     f1[h // 2, w // 2, :3] ^= 0xC3
     ofmt = {"NV12": 0, "I420": 1}[fmt]
-    lib = _abi.load()
-    try:
-        lib.sk_set_kernel_variant(100 if generic else 101)
-        with PreencodeSession(w, h, out_width=ow, out_height=oh, out_format=fmt, colorimetry=1, chroma_site=site,
-                              scale_variant=var) as s:
-            prev = None
-            for i, f in enumerate((f0, f1)):
-                r = s.convert(f, slot=i & 1)
-                e = o.convert(f, ow, oh, out_fmt=ofmt, matrix=1, chroma_site=site, scale_variant=var)
-                assert (r.frame == e).all()
-                em, en = o.damage(ow, oh, ofmt, e, prev)
-                assert (r.damage_map == em).all() and r.damaged_count == en
-                prev = e
-    finally:
-        lib.sk_set_kernel_variant(101)
+    with PreencodeSession(w, h, out_width=ow, out_height=oh, out_format=fmt, colorimetry=1, chroma_site=site,
+                          scale_variant=var, scale_generic=generic) as s:
+        prev = None
+        for i, f in enumerate((f0, f1)):
+            r = s.convert(f, slot=i & 1)
+            e = o.convert(f, ow, oh, out_fmt=ofmt, matrix=1, chroma_site=site, scale_variant=var)
+            assert (r.frame == e).all()
+            em, en = o.damage(ow, oh, ofmt, e, prev)
+            assert (r.damage_map == em).all() and r.damaged_count == en
+            prev = e
