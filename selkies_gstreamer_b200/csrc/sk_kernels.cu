@@ -396,6 +396,7 @@ sk_convert_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBa
     const int y0 = by0 + warp * ROWS;
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 * QX <= g.out_w) && (by0 + 16 * RP <= g.out_h);
+    if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
 
     uint32_t pol_state = 0;
     if (DAMAGE && POLICY) {
@@ -489,6 +490,7 @@ sk_convert_warp_kernel(const __grid_constant__ SkGeom g, const __grid_constant__
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 256 <= g.out_w) && (by0 + 16 <= g.out_h);
 
+    if (DAMAGE && blockIdx.x == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
     uint32_t pol_state = 0;
     if (DAMAGE && POLICY) pol_state = policy_prefetch(f, g, lane < 16, tx * 16 + lane, ty);
 
@@ -593,6 +595,7 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
     const bool rows_valid = y0 < h;
     const int nv = rows_valid ? nvx : 0;
     const bool have_prev = DAMAGE && (f.prev != nullptr);
+    if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
 
     uint32_t hh[2][2];
     uint32_t diff = 0;
@@ -947,6 +950,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     __shared__ __align__(8) unsigned long long s_bar;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) mbar_init(bar, 1);
+    if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
     __syncthreads();
     const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8, blockIdx.x * 8 + threadIdx.x, blockIdx.y) : 0u;
     uint32_t diff = 0;
@@ -996,6 +1000,7 @@ sk_gather_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkGat
 {
     const int bx = blockIdx.x * kThreads + threadIdx.x;
     const int by = blockIdx.y;
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0 && a.blocks_zero != nullptr) *a.blocks_zero = 0u;
     bool need = false;
     if (bx < g.mb_w) {
         const size_t idx = (size_t)by * g.mb_w + bx;

@@ -36,7 +36,10 @@ struct SkFrame {
     uint8_t *out;             // packed output frame being written
     const uint8_t *prev;      // previous packed output frame, or nullptr (all damaged)
     uint8_t *map;             // [mb_h][mb_w]
-    uint32_t *count_out;      // damaged-block count of this frame (written by the last CTA)
+    uint32_t *count_out;      // damaged-block count of this frame: CTAs add to it, it must start at zero
+    uint32_t *count_zero;     // the word the NEXT use of this ring entry will add to: zeroed by this launch, so
+                              // that no memset has to be queued in front of any launch (nullptr: nothing to zero)
+    int count_zero_n;         // words to zero there: 1, or a whole set when this frame leads a batch
     uint32_t *scratch;        // [0] running count, [1] CTA ticket; both return to 0 at kernel end
     const int32_t *v_off;     // scale: first source row per output row
     const int16_t *v_tap;     // scale: second vertical tap (6-bit) per output row
@@ -55,7 +58,8 @@ struct SkGather {
     const uint8_t *map;       // this frame's damage map [mb_h][mb_w], or nullptr (copy everything)
     uint8_t *stale;           // [n_ring][mb_h][mb_w]: blocks each host frame has missed so far
     int n_ring, ring_idx;
-    uint32_t *blocks_out;     // += number of macroblocks written (zeroed on the stream by the caller)
+    uint32_t *blocks_out;     // += number of macroblocks written (starts at zero)
+    uint32_t *blocks_zero;    // the word the next use of this ring entry adds to: zeroed here
 };
 cudaError_t sk_launch_gather(const SkGeom &g, const SkGather &a, cudaStream_t st);
 cudaError_t sk_preload_scale_generic();

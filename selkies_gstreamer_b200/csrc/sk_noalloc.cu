@@ -151,6 +151,8 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
     b.f[0].prev = static_cast<const uint8_t *>(d_prev);
     b.f[0].map = d_map;
     b.f[0].count_out = d_count;
+    b.f[0].count_zero = nullptr;        // the ticket scheme below publishes the total; nothing to pre-zero
+    b.f[0].count_zero_n = 0;
     b.f[0].scratch = d_counters;
     b.f[0].v_off = d_off;
     b.f[0].v_tap = d_tap;

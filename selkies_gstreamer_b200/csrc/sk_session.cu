@@ -28,7 +28,14 @@ static_assert(sizeof(sk_result) == 144 && sizeof(sk_config) == 72, "ABI structs 
 namespace {
 
 constexpr int kMaxInflight = 8;
-constexpr size_t kCountHdr = 128;      // counts (one u32 per batch member) in front of the maps of a meta block
+// Header in front of the maps of a meta block: two alternating sets of count words (one u32 per batch
+// member each) and two alternating gathered-block words.  A use of the block adds into one set and zeroes
+// the other inside the same kernel, so no memset is ever queued in front of a launch: the previous use
+// of the same block — the only reader of the set being zeroed — has finished its read-back by then
+// (that is the ring-entry dependency every submission waits on anyway).
+constexpr size_t kCountHdr = 512;
+constexpr int kCountSet = 32;           // words per set (SK_MAX_BATCH)
+constexpr int kGatherWord = 64;         // first of the two gathered-block words
 std::atomic<uint64_t> g_launches{0};
 std::atomic<int> g_variant{0};         // tuning build only (sk_tuning_set_variant); the release library has one shape
 std::atomic<int> g_snake{1};            // alternate traversal direction per launch (tuning build: 102 off / 103 on)
@@ -65,6 +72,8 @@ struct Ring {          // one output ring entry (submission order)
     uint8_t *h_out_user = nullptr;    // caller's output buffer of this frame (sk_submit_io), else nullptr
     uint8_t *h_out_dev = nullptr;     // device-visible address of h_out (mapped; gated read-back)
     bool gated = false;               // this frame came back through the gather kernel
+    unsigned use = 0;                 // how often this entry's own meta block has been used (picks the count set)
+    const uint32_t *h_blocks = nullptr; // gathered-block count of this frame in pinned memory
     const uint32_t *h_count = nullptr; // this frame's damaged-block count in pinned memory
     const uint32_t *d_count = nullptr; // ... and where the kernel adds it up in HBM
 };
@@ -88,6 +97,7 @@ struct sk_session {
     uint32_t *d_state = nullptr;      // per-macroblock temporal policy state
     uint8_t *d_stale = nullptr;       // gated read-back: [n][mb_h*mb_w] blocks each host frame has missed
     bool bmeta_ready = false;         // leader: d_bmeta/h_bmeta allocated for every ring entry
+    unsigned bmeta_use[kMaxInflight] = {};  // leader: uses of each batch block (picks the count set)
     uint8_t *d_bmeta[kMaxInflight] = {};   // leader only: maps of all batch members, contiguous per ring entry
     uint8_t *h_bmeta[kMaxInflight] = {};
     int32_t *d_voff = nullptr;
@@ -205,10 +215,13 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.prev = (s->prev_ring >= 0) ? s->ring[s->prev_ring].d_out : nullptr;
     r.d_meta_view = r.d_meta + kCountHdr;
     r.h_meta_view = r.h_meta + kCountHdr;
-    r.h_count = reinterpret_cast<const uint32_t *>(r.h_meta);
-    r.d_count = reinterpret_cast<const uint32_t *>(r.d_meta);
+    const unsigned set = r.use & 1u;                           // provisional: a batch on the leader's block overrides it
+    r.h_count = reinterpret_cast<const uint32_t *>(r.h_meta) + set * kCountSet;
+    r.d_count = reinterpret_cast<const uint32_t *>(r.d_meta) + set * kCountSet;
     f.map = r.d_meta_view;
-    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta);     // zeroed on the stream before the launch
+    f.count_out = reinterpret_cast<uint32_t *>(r.d_meta) + set * kCountSet;
+    f.count_zero = reinterpret_cast<uint32_t *>(r.d_meta) + (set ^ 1u) * kCountSet;
+    f.count_zero_n = 1;
     f.state = s->d_state;                       // nullptr unless SK_FLAG_POLICY
     f.policy = r.d_meta_view + s->map_bytes;
     f.scratch = nullptr;
@@ -295,11 +308,14 @@ int enqueue_frame_readback(sk_session *err_to, sk_session *s, int ri, cudaStream
         a.stale = s->d_stale;
         a.n_ring = s->n;
         a.ring_idx = ri;
-        a.blocks_out = reinterpret_cast<uint32_t *>(r.d_meta) + 1;     // zeroed together with the count
+        a.blocks_out = reinterpret_cast<uint32_t *>(r.d_meta) + kGatherWord + (r.use & 1u);
+        a.blocks_zero = reinterpret_cast<uint32_t *>(r.d_meta) + kGatherWord + ((r.use & 1u) ^ 1u);
+        r.h_blocks = reinterpret_cast<const uint32_t *>(r.h_meta) + kGatherWord + (r.use & 1u);
         g_launches.fetch_add(1, std::memory_order_relaxed);
         SK_CUDA(err_to, sk_launch_gather(s->geom, a, st));
         r.gated = true;
     }
+    if (own_meta) r.use++;             // the entry's own block has now been used once more
     if (damage && own_meta)
         SK_CUDA(err_to, cudaMemcpyAsync(r.h_meta, r.d_meta, kCountHdr + (s->d_state ? s->meta_bytes : s->map_bytes),
                                         cudaMemcpyDeviceToHost, st));
@@ -323,12 +339,13 @@ int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot,
 
     SkBatch b;
     const int ri = stage_frame(s, d_in, frame_id, b.f[0]);
-    if (!(s->cfg.flags & SK_FLAG_NO_DAMAGE)) SK_CUDA(s, cudaMemsetAsync(r.d_meta, 0, 8, s->s_comp));
     if (timing) SK_CUDA(s, cudaEventRecord(r.k_start, s->s_comp));
     cudaError_t le = launch(s, g, b, 1, s->s_comp);
     if (le != cudaSuccess) {
         s->prev_ring = -1;          // the ring entry was never written: the next frame has no predecessor
         r.valid = false;
+        cudaGetLastError();
+        cudaMemset(r.d_meta, 0, kCountHdr);     // the launch that would have zeroed the next count word never ran
         return fail(s, SK_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(le));
     }
     SK_CUDA(s, cudaEventRecord(r.k_done, s->s_comp));
@@ -390,6 +407,7 @@ int prepare_bmeta(sk_session *L)
     for (int k = 0; k < L->n; k++) {
         cudaError_t e = cudaSuccess;
         if (!L->d_bmeta[k]) e = cudaMalloc((void **)&L->d_bmeta[k], bytes);
+        if (e == cudaSuccess) e = cudaMemset(L->d_bmeta[k], 0, kCountHdr);
         if (e == cudaSuccess && !L->h_bmeta[k]) e = cudaHostAlloc((void **)&L->h_bmeta[k], bytes, cudaHostAllocDefault);
         if (e != cudaSuccess) {
             cudaGetLastError();
@@ -407,8 +425,14 @@ int prepare_bmeta(sk_session *L)
 // A batch step failed after some members' rings were advanced: their next frame has no predecessor.
 void abandon_batch(sk_session **ss, int n)
 {
+    cudaGetLastError();
     for (int i = 0; i < n; i++) {
         ss[i]->prev_ring = -1;
+        // count words must start at zero again: the launch that would have zeroed them never ran
+        for (int k = 0; k < ss[i]->n; k++) {
+            cudaMemset(ss[i]->ring[k].d_meta, 0, kCountHdr);
+            if (ss[i]->d_bmeta[k]) cudaMemset(ss[i]->d_bmeta[k], 0, kCountHdr);
+        }
         for (int k = 0; k < ss[i]->n; k++)
             if (ss[i]->ring[k].valid && !ss[i]->ring[k].used) ss[i]->ring[k].valid = false;
     }
@@ -760,9 +784,14 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
             Ring &r = ss[i]->ring[ris[i]];
             r.d_meta_view = L->d_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
             r.h_meta_view = L->h_bmeta[lri] + kCountHdr + (size_t)i * L->meta_bytes;
-            r.h_count = reinterpret_cast<const uint32_t *>(L->h_bmeta[lri]) + i;
-            r.d_count = reinterpret_cast<const uint32_t *>(L->d_bmeta[lri]) + i;
-            b.f[i].count_out = reinterpret_cast<uint32_t *>(L->d_bmeta[lri]) + i;
+            const unsigned set = L->bmeta_use[lri] & 1u;
+            r.h_count = reinterpret_cast<const uint32_t *>(L->h_bmeta[lri]) + set * kCountSet + i;
+            r.d_count = reinterpret_cast<const uint32_t *>(L->d_bmeta[lri]) + set * kCountSet + i;
+            b.f[i].count_out = reinterpret_cast<uint32_t *>(L->d_bmeta[lri]) + set * kCountSet + i;
+            // the other set is zeroed for the block's next use — all of it, by the first member's frame:
+            // the next batch may have more members than this one
+            b.f[i].count_zero = i == 0 ? reinterpret_cast<uint32_t *>(L->d_bmeta[lri]) + (set ^ 1u) * kCountSet : nullptr;
+            b.f[i].count_zero_n = i == 0 ? kCountSet : 0;
             b.f[i].map = r.d_meta_view;
             b.f[i].policy = r.d_meta_view + L->map_bytes;
         }
@@ -775,7 +804,7 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
             return fail(L, SK_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
         }                                                                                            \
     } while (0)
-    if (damage) SK_BATCH_CUDA(cudaMemsetAsync(L->d_bmeta[lri], 0, kCountHdr, L->s_comp));
+    if (damage) L->bmeta_use[lri]++;
     if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
     SK_BATCH_CUDA(launch(L, g, b, n, L->s_comp));
     SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
@@ -817,7 +846,6 @@ int sk_batch_submit_host(sk_session **ss, int n, const void *const *host_in, siz
     SK_CUDA(L, cudaSetDevice(L->dev));
 
     const bool timing = L->cfg.flags & SK_FLAG_TIMING;
-    const bool damage = !(L->cfg.flags & SK_FLAG_NO_DAMAGE);
     SkBatch b;
     int ris[SK_MAX_BATCH];
     int slots[SK_MAX_BATCH];
@@ -836,9 +864,6 @@ int sk_batch_submit_host(sk_session **ss, int n, const void *const *host_in, siz
         ris[i] = stage_frame(s, s->slots[slots[i]].d_in, frame_id, b.f[i]);
     }
     Ring &lr = L->ring[ris[0]];
-    if (damage)
-        for (int i = 0; i < n; i++)
-            SK_BATCH_CUDA(cudaMemsetAsync(ss[i]->ring[ris[i]].d_meta, 0, 8, L->s_comp));
     if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
     SK_BATCH_CUDA(launch(L, L->geom, b, n, L->s_comp));
     SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
@@ -890,7 +915,7 @@ void describe(sk_session *s, Ring &r, uint64_t frame_id, sk_result *out, bool ho
     if (r.h_out_user) out->host_frame = r.h_out_user;
     else if (s->cfg.flags & SK_FLAG_HOST_OUTPUT) out->host_frame = r.h_out;
     if (out->host_frame)
-        out->readback_bytes = r.gated ? (uint64_t)reinterpret_cast<const uint32_t *>(r.h_meta)[1] * 384u : s->frame_bytes;
+        out->readback_bytes = r.gated ? (uint64_t)*r.h_blocks * 384u : s->frame_bytes;
     if (damage) {
         out->host_damage_map = r.h_meta_view;
         out->damaged_count = *r.h_count;

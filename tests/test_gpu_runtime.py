@@ -114,7 +114,7 @@ class _RawDeviceBytes:
     """A raw device address dressed up for torch.as_tensor (CUDA array interface v2: no stream sync)."""
 
     def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), True), "version": 2}
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
 
 
 def _device_view(torch, ptr, nbytes):

@@ -86,6 +86,13 @@ def _run_pair(lib, torch, frames, w, h, ow, oh, fmt, matrix, site, *, in_fmt=0, 
     return got
 
 
+def _same_pixels(a, b, w, h, fmt):
+    """Equal on every pixel of every plane.  Row-padding bytes (strides are rounded up to 4) are not
+    compared: the kernel never writes them, and here the buffers are the caller's, pre-filled with 0xEE."""
+    from oracle import cpu_oracle as o
+    return all(np.array_equal(x, y) for x, y in zip(o.split_planes(a, w, h, FMT[fmt]), o.split_planes(b, w, h, FMT[fmt])))
+
+
 def _need_gpu():
     torch = pytest.importorskip("torch")
     if not torch.cuda.is_available():
@@ -134,11 +141,12 @@ def test_noalloc_padded_rows_rgbx_and_convert_only():
     got = _run_pair(lib, torch, [f0, f1], w, h, ow, oh, "NV12", 0, 0, in_fmt=1, pad_px=37, device_id=0)
     for i, ((gf, gm, gc), (wf, wm, wc)) in enumerate(zip(got, want)):
         assert np.array_equal(gf, wf) and np.array_equal(gm, wm) and gc == wc, f"call {i}"
-    # convert only: the map and count buffers may be NULL and stay untouched
+    # convert only: the map and count buffers may be NULL and stay untouched (802 wide: the I420 chroma
+    # rows carry 3 bytes of padding each)
     want = _oracle_reference([f0, f1], w, h, w, h, "I420", 2, 1, damage=False)
     got = _run_pair(lib, torch, [f0, f1], w, h, w, h, "I420", 2, 1, damage=False, pad_px=3)
     for i, ((gf, gm, gc), (wf, _, _)) in enumerate(zip(got, want)):
-        assert np.array_equal(gf, wf), f"call {i}"
+        assert _same_pixels(gf, wf, w, h, "I420"), f"call {i}"
         assert (gm == 0x77).all() and gc == -1
 
 

@@ -1,6 +1,8 @@
 #!/usr/bin/env python3
 """Run one geometry device-resident for a few steps (ncu target).
-    python tools/run_config.py W H OW OH FMT BATCH STEPS"""
+    python tools/run_config.py W H OW OH FMT BATCH STEPS [VARIANT]
+VARIANT needs the tuning build: make -C selkies_gstreamer_b200/csrc tuning;
+SELKIES_PREENCODE_LIB=selkies_gstreamer_b200/libselkies_preencode_tuning.so"""
 import os
 import sys
 
@@ -13,9 +15,9 @@ w, h, ow, oh = (int(x) for x in sys.argv[1:5])
 fmt, batch, steps = sys.argv[5], int(sys.argv[6]), int(sys.argv[7])
 if len(sys.argv) > 8:
     from selkies_gstreamer_b200 import _abi
-    _abi.load().sk_set_kernel_variant(int(sys.argv[8]))
+    _abi.load().sk_tuning_set_variant(int(sys.argv[8]))
 sess = [sk.PreencodeSession(w, h, out_width=ow, out_height=oh, out_format=fmt, colorimetry="bt709",
-                            chroma_site="mpeg2", host_output=False, timing=(i == 0)) for i in range(batch)]
+                            chroma_site="mpeg2", host_output=False, timing=(i == 0), spin_wait=True) for i in range(batch)]
 base = synth.desktop(w, h)
 nxt = synth.mutate(base, 0.05, seed=1, aligned=False)
 for s in sess:
