@@ -80,6 +80,24 @@ enum {
                                       or a caller-supplied output buffer.                               */
 };
 
+/* sk_config.parity_switches — one bit per recollection of upstream GStreamer that this restatement
+ * could have wrong.  0 = the arithmetic as restated, and the fast kernels.
+ * GStreamer 1.24.12 (the reference's pin, addons/gstreamer/Dockerfile:85-93) cannot be run where this
+ * was built; whoever can, produces golden vectors with tools/make_gst_golden.py and
+ * tests/test_gst_golden.py then either passes or names the bit that makes it pass.  Bits 0,2,3,4 change
+ * per-pixel arithmetic and route the session through the generic kernel (slower, same traffic) until
+ * the fast kernels are updated to the confirmed behaviour; bits 1,5,6 only change host-derived
+ * constants and keep the fast kernels. */
+enum {
+    SK_PS_MATRIX_ROUND   = 1 << 0,  /* R8: +128 rounding term before the >>8 of the 8-bit matrix           */
+    SK_PS_COEFF_HALF_UP  = 1 << 1,  /* R8: coefficients rounded half away from zero instead of rint()      */
+    SK_PS_CS_EDGE_KEEP   = 1 << 2,  /* R3: cosited filter leaves the first and last chroma sample as is    */
+    SK_PS_CHROMA_V_FIRST = 1 << 3,  /* R4: vertical average first, horizontal filter second                */
+    SK_PS_CHROMA_BOX4    = 1 << 4,  /* R4: chroma-site none: (a+b+c+d+2)>>2 in one rounding                */
+    SK_PS_HINC_PLAIN     = 1 << 5,  /* R6: horizontal increment without the "-1"                           */
+    SK_PS_V_FIRST_ON_TIE = 1 << 6   /* R7: equal cost of the two scale orders goes to vertical first       */
+};
+
 typedef struct sk_session sk_session;
 
 /*
@@ -105,6 +123,7 @@ typedef struct sk_config {
     int32_t  damage_block_threshold;     /* consecutive damaged frames that make a block "hot" (10) */
     int32_t  damage_block_duration;      /* frames a hot block stays hot after its last change (20) */
     int32_t  paint_over_trigger_frames;  /* still frames after which a changed block is repainted (15) */
+    uint32_t parity_switches;            /* SK_PS_*; 0 = as restated                                    */
 } sk_config;
 
 /* Per-macroblock policy flags (sk_result.host_policy_map), updated inside the convert kernel. */

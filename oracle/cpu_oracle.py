@@ -19,12 +19,17 @@ OUT_NV12, OUT_I420 = 0, 1
 MATRIX_BT601, MATRIX_BT709, MATRIX_BT2020 = 0, 1, 2
 SITE_NONE, SITE_H_COSITED = 0, 1
 SCALE_GST_LQ, SCALE_PLAIN_LQ = 0, 1
+# parity switches (sk_oracle.h SKO_PS_*; the product's SK_PS_* bits have the same values)
+PS_MATRIX_ROUND, PS_COEFF_HALF_UP, PS_CS_EDGE_KEEP, PS_CHROMA_V_FIRST, PS_CHROMA_BOX4, PS_HINC_PLAIN, PS_V_FIRST_ON_TIE = (
+    1, 2, 4, 8, 16, 32, 64)
+PS_ALL = {"matrix-round": 1, "coeff-half-up": 2, "cs-edge-keep": 4, "chroma-v-first": 8, "chroma-box4": 16,
+          "hinc-plain": 32, "v-first-on-tie": 64}
 
 
 class SkoConfig(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int) for n in (
         "in_w", "in_h", "in_stride", "in_fmt", "out_w", "out_h", "out_fmt",
-        "matrix", "chroma_site", "scale_variant", "n_threads")]
+        "matrix", "chroma_site", "scale_variant", "n_threads", "switches")]
 
 
 def build(force: bool = False) -> str:
@@ -55,6 +60,10 @@ def lib() -> ctypes.CDLL:
             ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_int)]
         L.sko_matrix_coeffs.restype = None
         L.sko_matrix_coeffs.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        L.sko_matrix_coeffs_sw.restype = None
+        L.sko_matrix_coeffs_sw.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        L.sko_h_increment_sw.restype = ctypes.c_int32
+        L.sko_h_increment_sw.argtypes = [ctypes.c_int] * 3
         L.sko_resampler_2tap.restype = None
         L.sko_resampler_2tap.argtypes = [ctypes.c_int] * 4 + [
             ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int16)]
@@ -90,9 +99,9 @@ def out_layout(w: int, h: int, fmt: int):
     return list(off), list(st)
 
 
-def matrix_coeffs(matrix: int) -> np.ndarray:
+def matrix_coeffs(matrix: int, switches: int = 0) -> np.ndarray:
     c = (ctypes.c_int * 12)()
-    lib().sko_matrix_coeffs(matrix, c)
+    lib().sko_matrix_coeffs_sw(matrix, switches, c)
     return np.array(list(c), dtype=np.int64).reshape(3, 4)
 
 
@@ -105,14 +114,14 @@ def resampler_2tap(in_size: int, out_size_: int, variant: int = SCALE_GST_LQ, pr
     return off, tap
 
 
-def h_increment(in_w: int, out_w: int) -> int:
-    return int(lib().sko_h_increment(in_w, out_w))
+def h_increment(in_w: int, out_w: int, switches: int = 0) -> int:
+    return int(lib().sko_h_increment_sw(in_w, out_w, switches))
 
 
 def convert(frame: np.ndarray, out_w: int | None = None, out_h: int | None = None, *,
             in_fmt: int = IN_BGRX, out_fmt: int = OUT_NV12, matrix: int = MATRIX_BT709,
             chroma_site: int = SITE_H_COSITED, scale_variant: int = SCALE_GST_LQ,
-            n_threads: int = 1) -> np.ndarray:
+            n_threads: int = 1, switches: int = 0) -> np.ndarray:
     """frame: uint8 [H, W, 4] (rows may be a strided view). Returns the packed output frame."""
     assert frame.dtype == np.uint8 and frame.ndim == 3 and frame.shape[2] == 4
     assert frame.strides[2] == 1 and frame.strides[1] == 4
@@ -120,7 +129,7 @@ def convert(frame: np.ndarray, out_w: int | None = None, out_h: int | None = Non
     out_w = out_w or w
     out_h = out_h or h
     cfg = SkoConfig(w, h, frame.strides[0], in_fmt, out_w, out_h, out_fmt, matrix,
-                    chroma_site, scale_variant, n_threads)
+                    chroma_site, scale_variant, n_threads, switches)
     out = np.zeros(out_size(out_w, out_h, out_fmt), dtype=np.uint8)
     rc = lib().sko_convert(ctypes.byref(cfg), _u8p(frame), _u8p(out))
     if rc != 0:

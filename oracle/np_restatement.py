@@ -24,11 +24,17 @@ def rgb_planes(frame: np.ndarray, in_fmt: str):
     return f[..., 0], f[..., 1], f[..., 2]
 
 
-def to_yuv444(r, g, b, matrix: str):
-    c = COEFFS[matrix]
+# Parity switches (sk_oracle.h SKO_PS_*): same bit values, independent implementation.
+PS_MATRIX_ROUND, PS_COEFF_HALF_UP, PS_CS_EDGE_KEEP, PS_CHROMA_V_FIRST, PS_CHROMA_BOX4, PS_HINC_PLAIN, PS_V_FIRST_ON_TIE = (
+    1, 2, 4, 8, 16, 32, 64)
+
+
+def to_yuv444(r, g, b, matrix: str, switches: int = 0):
+    c = COEFFS[matrix]          # none of the 27 coefficients sits near a tie: PS_COEFF_HALF_UP changes nothing
+    rnd = 128 if switches & PS_MATRIX_ROUND else 0
     out = []
     for i in range(3):
-        out.append((c[i, 0] * r + c[i, 1] * g + c[i, 2] * b + c[i, 3]) >> 8)
+        out.append((c[i, 0] * r + c[i, 1] * g + c[i, 2] * b + c[i, 3] + rnd) >> 8)
     return out
 
 
@@ -36,21 +42,34 @@ def avg(a, b):
     return (a + b + 1) >> 1
 
 
-def chroma_420(c: np.ndarray, site: str) -> np.ndarray:
-    """c: int64 [H, W] full-resolution chroma; returns [H/2, W/2]."""
-    h, w = c.shape
+def _h_filter(c: np.ndarray, site: str, switches: int) -> np.ndarray:
+    """[H, W] -> [H, W/2]: the horizontal half of the 4:2:0 down-sampling."""
+    w = c.shape[1]
     if site == "none":
-        hh = avg(c[:, 0::2], c[:, 1::2])
-    else:
-        ce = c[:, 0::2]            # even samples
-        co = c[:, 1::2]            # odd samples (never modified upstream)
-        left = np.empty_like(ce)
-        left[:, 1:] = co[:, :-1]
-        left[:, 0] = ce[:, 0]      # [3 1] opening tap == [1 2 1] with left := centre
-        right = co.copy()
-        if w > 2:                  # W == 2: only the opening tap runs upstream
-            right[:, -1] = ce[:, -1]   # [1 3] closing tap == [1 2 1] with right := centre
-        hh = (left + 2 * ce + right + 2) >> 2
+        return avg(c[:, 0::2], c[:, 1::2])
+    ce = c[:, 0::2]            # even samples
+    co = c[:, 1::2]            # odd samples (never modified upstream)
+    left = np.empty_like(ce)
+    left[:, 1:] = co[:, :-1]
+    left[:, 0] = ce[:, 0]      # [3 1] opening tap == [1 2 1] with left := centre
+    right = co.copy()
+    if w > 2:                  # W == 2: only the opening tap runs upstream
+        right[:, -1] = ce[:, -1]   # [1 3] closing tap == [1 2 1] with right := centre
+    hh = (left + 2 * ce + right + 2) >> 2
+    if switches & PS_CS_EDGE_KEEP:
+        hh[:, 0] = ce[:, 0]
+        if w > 2:
+            hh[:, -1] = ce[:, -1]
+    return hh
+
+
+def chroma_420(c: np.ndarray, site: str, switches: int = 0) -> np.ndarray:
+    """c: int64 [H, W] full-resolution chroma; returns [H/2, W/2]."""
+    if site == "none" and switches & PS_CHROMA_BOX4:
+        return (c[0::2, 0::2] + c[0::2, 1::2] + c[1::2, 0::2] + c[1::2, 1::2] + 2) >> 2
+    if switches & PS_CHROMA_V_FIRST:
+        return _h_filter(avg(c[0::2, :], c[1::2, :]), site, switches)
+    hh = _h_filter(c, site, switches)
     return avg(hh[0::2, :], hh[1::2, :])
 
 
@@ -77,7 +96,7 @@ def scale_2tap_lq(rgb: np.ndarray, out_w: int, out_h: int, v_off, v_tap, h_inc: 
 
 
 def convert(frame: np.ndarray, *, in_fmt="BGRx", out_fmt="NV12", matrix="bt709", site="h-cosited",
-            out_w=None, out_h=None, v_off=None, v_tap=None, h_inc=0):
+            out_w=None, out_h=None, v_off=None, v_tap=None, h_inc=0, switches=0):
     """Returns (Y[H,W], U[H/2,W/2], V[H/2,W/2]) as uint8 — layout-free."""
     h, w = frame.shape[:2]
     out_w = out_w or w
@@ -86,11 +105,13 @@ def convert(frame: np.ndarray, *, in_fmt="BGRx", out_fmt="NV12", matrix="bt709",
     if (out_w, out_h) != (w, h):
         rgb = np.stack([r, g, b], axis=-1)
         h_first = out_w * h <= w * out_h
+        if switches & PS_V_FIRST_ON_TIE and out_w * h == w * out_h:
+            h_first = False
         rgb = scale_2tap_lq(rgb, out_w, out_h, v_off, v_tap, h_inc, h_first)
         r, g, b = rgb[..., 0], rgb[..., 1], rgb[..., 2]
-    y, u, v = to_yuv444(r, g, b, matrix)
+    y, u, v = to_yuv444(r, g, b, matrix, switches)
     assert y.min() >= 0 and y.max() <= 255 and u.min() >= 0 and u.max() <= 255 and v.min() >= 0 and v.max() <= 255
-    return (y.astype(np.uint8), chroma_420(u, site).astype(np.uint8), chroma_420(v, site).astype(np.uint8))
+    return (y.astype(np.uint8), chroma_420(u, site, switches).astype(np.uint8), chroma_420(v, site, switches).astype(np.uint8))
 
 
 def damage(y, u, v, py, pu, pv):

@@ -82,6 +82,11 @@ static void kr_kb(int matrix, double *kr, double *kb)
  */
 void sko_matrix_coeffs(int matrix, int c[3][4])
 {
+    sko_matrix_coeffs_sw(matrix, 0, c);
+}
+
+void sko_matrix_coeffs_sw(int matrix, int switches, int c[3][4])
+{
     double kr, kb, kg, x, m[3][4];
     const double in_scale = 1 / ((float)255);
     const double sc[3] = {(float)219, (float)224, (float)224};
@@ -100,7 +105,9 @@ void sko_matrix_coeffs(int matrix, int c[3][4])
             m[i][j] = m[i][j] * in_scale * sc[i] * 256.0;
         m[i][3] = of[i] * 256.0;
         for (j = 0; j < 4; j++)
-            c[i][j] = (int)rint(m[i][j]);
+            c[i][j] = (switches & SKO_PS_COEFF_HALF_UP) ? (int)round(m[i][j]) : (int)rint(m[i][j]);
+        if (switches & SKO_PS_MATRIX_ROUND)
+            c[i][3] += 128;          /* R8: round to nearest at the >>8 instead of flooring */
     }
 }
 
@@ -110,10 +117,10 @@ typedef struct {
 
 /* video-converter.c: videoconvert_convert_init_tables() — three 16-bit lanes
  * accumulated in one int64 per channel value. */
-static void init_tables(matrix_tables *t, int matrix)
+static void init_tables(matrix_tables *t, int matrix, int switches)
 {
     int c[3][4], i, j;
-    sko_matrix_coeffs(matrix, c);
+    sko_matrix_coeffs_sw(matrix, switches, c);
     for (i = 0; i < 256; i++) {
         int64_t r = 0, g = 0, b = 0;
         for (j = 0; j < 3; j++) {
@@ -179,19 +186,34 @@ void sko_chroma_down_h2(uint8_t *p, int w)
 
 /* video-chroma.c: video_chroma_down_h2_cs_u8 — [3 1] at x=0, [1 2 1] at even x,
  * [1 3] closing tap; odd samples stay original while the loop runs. */
-void sko_chroma_down_h2_cs(uint8_t *p, int w)
+static void chroma_down_h2_cs_sw(uint8_t *p, int w, int keep_edges)
 {
     int i, k;
     if (w < 2)
         return;
-    for (k = 2; k <= 3; k++)
-        p[k] = F31(p[k], p[4 + k]);
+    if (!keep_edges)
+        for (k = 2; k <= 3; k++)
+            p[k] = F31(p[k], p[4 + k]);
     for (i = 2; i < w - 2; i += 2)
         for (k = 2; k <= 3; k++)
             p[4 * i + k] = F121(p[4 * (i - 1) + k], p[4 * i + k], p[4 * (i + 1) + k]);
-    if (i < w)
+    if (i < w && !keep_edges)
         for (k = 2; k <= 3; k++)
             p[4 * i + k] = F31(p[4 * i + k], p[4 * (i - 1) + k]);
+}
+
+void sko_chroma_down_h2_cs(uint8_t *p, int w)
+{
+    chroma_down_h2_cs_sw(p, w, 0);
+}
+
+/* R4 alternative for site none: both pairs of both lines in one rounding. */
+static void chroma_down_box4(uint8_t *l0, const uint8_t *l1, int w)
+{
+    int i, k;
+    for (i = 0; i + 1 < w; i += 2)
+        for (k = 2; k <= 3; k++)
+            l0[4 * i + k] = (uint8_t)((l0[4 * i + k] + l0[4 * i + 4 + k] + l1[4 * i + k] + l1[4 * i + 4 + k] + 2) >> 2);
 }
 
 /* video-orc.orc: video_orc_chroma_down_v2_u8 — avgub of U,V of two lines into
@@ -210,9 +232,14 @@ void sko_chroma_down_v2(uint8_t *l0, const uint8_t *l1, int w)
 /* video-scaler.c: gst_video_scaler_new() — scale->inc for the 2-tap h path. */
 int32_t sko_h_increment(int in_w, int out_w)
 {
+    return sko_h_increment_sw(in_w, out_w, 0);
+}
+
+int32_t sko_h_increment_sw(int in_w, int out_w, int switches)
+{
     if (out_w == 1)
         return 0;
-    return (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - 1);
+    return (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - ((switches & SKO_PS_HINC_PLAIN) ? 0 : 1));
 }
 
 /* video-orc.orc: video_orc_resample_h_2tap_4u8_lq == ldreslinl d, s, 0, inc. */
@@ -422,15 +449,27 @@ static void *band_main(void *arg)
         make_ayuv_line(j, y, l0, tmp);
         if (have2)
             make_ayuv_line(j, y + 1, l1, tmp);
-        if (c->chroma_site == SKO_SITE_H_COSITED) {
-            sko_chroma_down_h2_cs(l0, c->out_w);
-            if (have2) sko_chroma_down_h2_cs(l1, c->out_w);
-        } else {
-            sko_chroma_down_h2(l0, c->out_w);
-            if (have2) sko_chroma_down_h2(l1, c->out_w);
+        {
+            const int keep = (c->switches & SKO_PS_CS_EDGE_KEEP) != 0;
+            const int cs = c->chroma_site == SKO_SITE_H_COSITED;
+            if (!cs && have2 && (c->switches & SKO_PS_CHROMA_BOX4)) {
+                chroma_down_box4(l0, l1, c->out_w);                    /* R4: one rounding */
+            } else if (have2 && (c->switches & SKO_PS_CHROMA_V_FIRST)) {
+                sko_chroma_down_v2(l0, l1, c->out_w);                   /* R4: vertical first ... */
+                if (cs) chroma_down_h2_cs_sw(l0, c->out_w, keep);       /* ... then horizontal */
+                else sko_chroma_down_h2(l0, c->out_w);
+            } else {
+                if (cs) {
+                    chroma_down_h2_cs_sw(l0, c->out_w, keep);
+                    if (have2) chroma_down_h2_cs_sw(l1, c->out_w, keep);
+                } else {
+                    sko_chroma_down_h2(l0, c->out_w);
+                    if (have2) sko_chroma_down_h2(l1, c->out_w);
+                }
+                if (have2)
+                    sko_chroma_down_v2(l0, l1, c->out_w);
+            }
         }
-        if (have2)
-            sko_chroma_down_v2(l0, l1, c->out_w);
         pack_pair(j, y, l0, have2 ? l1 : NULL);
     }
     free(l0);
@@ -454,13 +493,15 @@ int sko_convert(const sko_config *cfg, const uint8_t *in, uint8_t *out)
 
     memset(&j, 0, sizeof j);
     j.cfg = cfg;  j.in = in;  j.out = out;
-    init_tables(&j.tab, cfg->matrix);
+    init_tables(&j.tab, cfg->matrix, cfg->switches);
     sko_out_layout(cfg->out_w, cfg->out_h, cfg->out_fmt, j.off, j.stride);
     j.scaling = (cfg->in_w != cfg->out_w) || (cfg->in_h != cfg->out_h);
     /* chain_scale(): h first when out_w*in_h <= in_w*out_h. */
     j.h_first = ((int64_t)cfg->out_w * cfg->in_h <= (int64_t)cfg->in_w * cfg->out_h);
+    if ((cfg->switches & SKO_PS_V_FIRST_ON_TIE) && (int64_t)cfg->out_w * cfg->in_h == (int64_t)cfg->in_w * cfg->out_h)
+        j.h_first = 0;                                                  /* R7 */
     if (j.scaling) {
-        j.h_inc = sko_h_increment(cfg->in_w, cfg->out_w);
+        j.h_inc = sko_h_increment_sw(cfg->in_w, cfg->out_w, cfg->switches);
         j.v_off = (int32_t *)malloc(sizeof(int32_t) * cfg->out_h);
         j.v_tap = (int16_t *)malloc(sizeof(int16_t) * cfg->out_h);
         sko_resampler_2tap(cfg->in_h, cfg->out_h, cfg->scale_variant, 6, j.v_off, j.v_tap);

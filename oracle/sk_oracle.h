@@ -35,6 +35,20 @@ enum { SKO_SITE_NONE = 0, SKO_SITE_H_COSITED = 1 };
  *            vertical weights (no stretch). */
 enum { SKO_SCALE_GST_LQ = 0, SKO_SCALE_PLAIN_LQ = 1 };
 
+/* Parity switches — one bit per recollection of upstream that could be wrong (SURVEY.md A.8 risk
+ * list); 0 = the restatement as written.  The product carries the same bits (sk_config.parity_switches,
+ * include/selkies_preencode.h) so that real GStreamer vectors, once somebody can produce them
+ * (tools/make_gst_golden.py), either turn parity green or name the bit to flip. */
+enum {
+    SKO_PS_MATRIX_ROUND   = 1 << 0,  /* R8: the 8-bit matrix adds a +128 rounding term before >>8           */
+    SKO_PS_COEFF_HALF_UP  = 1 << 1,  /* R8: coefficients rounded half away from zero instead of rint()      */
+    SKO_PS_CS_EDGE_KEEP   = 1 << 2,  /* R3: the cosited filter leaves the first and last sample unfiltered  */
+    SKO_PS_CHROMA_V_FIRST = 1 << 3,  /* R4: vertical average first, horizontal filter second                */
+    SKO_PS_CHROMA_BOX4    = 1 << 4,  /* R4: site none: one rounding, (a+b+c+d+2)>>2, not cascaded averages  */
+    SKO_PS_HINC_PLAIN     = 1 << 5,  /* R6: horizontal increment ((in-1)<<16)/(out-1) without the "-1"      */
+    SKO_PS_V_FIRST_ON_TIE = 1 << 6   /* R7: equal cost of the two pass orders goes to vertical first        */
+};
+
 typedef struct sko_config {
     int in_w, in_h;
     int in_stride;      /* bytes; >= 4*in_w */
@@ -45,6 +59,7 @@ typedef struct sko_config {
     int chroma_site;
     int scale_variant;
     int n_threads;      /* row bands, as videoconvert n-threads; <=1 means serial */
+    int switches;       /* SKO_PS_* */
 } sko_config;
 
 /* Size of the packed output frame in GstVideoInfo default layout. */
@@ -55,6 +70,7 @@ void sko_out_layout(int out_w, int out_h, int out_fmt,
 
 /* The 3x4 integer matrix (8 fractional bits) for [Y,U,V] rows x [R,G,B,offset]. */
 void sko_matrix_coeffs(int matrix, int coeffs[3][4]);
+void sko_matrix_coeffs_sw(int matrix, int switches, int coeffs[3][4]);
 
 /* Vertical / generic 2-tap tables of the resampler: for each of out_size
  * outputs the first source index and the s16 second tap at `precision` bits. */
@@ -62,6 +78,7 @@ void sko_resampler_2tap(int in_size, int out_size, int variant, int precision,
                         int32_t *offset, int16_t *tap1);
 /* Horizontal edge-aligned increment (16.16). */
 int32_t sko_h_increment(int in_w, int out_w);
+int32_t sko_h_increment_sw(int in_w, int out_w, int switches);
 
 /* Convert (+scale) one frame. Returns 0 or a negative error. */
 int sko_convert(const sko_config *cfg, const uint8_t *in, uint8_t *out);

@@ -24,6 +24,8 @@ SK_SCALE_BILINEAR = 1
 SK_SCALE_VARIANT_GST_LQ, SK_SCALE_VARIANT_PLAIN_LQ = 0, 1
 SK_FLAG_NO_DAMAGE, SK_FLAG_HOST_OUTPUT, SK_FLAG_TIMING, SK_FLAG_POLICY = 1, 2, 4, 8
 SK_FLAG_SCALE_GENERIC, SK_FLAG_SPIN_WAIT, SK_FLAG_GATED_READBACK = 16, 32, 64
+SK_PS_MATRIX_ROUND, SK_PS_COEFF_HALF_UP, SK_PS_CS_EDGE_KEEP, SK_PS_CHROMA_V_FIRST = 1, 2, 4, 8
+SK_PS_CHROMA_BOX4, SK_PS_HINC_PLAIN, SK_PS_V_FIRST_ON_TIE = 16, 32, 64
 SK_MAX_BATCH = 32
 SK_ABI_VERSION = 3
 SK_POLICY_DAMAGED, SK_POLICY_HOT, SK_POLICY_PAINT_OVER = 1, 2, 4
@@ -58,6 +60,7 @@ class SkConfig(ctypes.Structure):
         ("damage_block_threshold", ctypes.c_int32),
         ("damage_block_duration", ctypes.c_int32),
         ("paint_over_trigger_frames", ctypes.c_int32),
+        ("parity_switches", ctypes.c_uint32),
     ]
 
 

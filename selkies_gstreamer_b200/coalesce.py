@@ -58,7 +58,7 @@ def batch_key(s: PreencodeSession):
     """Sessions with equal keys may share a launch (sk_batch_submit's own rule)."""
     f = s.flags & (_abi.SK_FLAG_NO_DAMAGE | _abi.SK_FLAG_POLICY | _abi.SK_FLAG_SCALE_GENERIC)
     return (s.device_index, s.width, s.height, s.in_stride, s.in_format.upper()[:3], s.out_width, s.out_height,
-            s.out_format, s.matrix, s.site, s.scale_variant, s.n_inflight, f, s.policy_knobs)
+            s.out_format, s.matrix, s.site, s.scale_variant, s.n_inflight, f, s.policy_knobs, s.parity_switches)
 
 
 class LaunchCoalescer:

@@ -27,10 +27,15 @@ MATRIX_NAMES = {_abi.SK_MATRIX_BT601: "bt601", _abi.SK_MATRIX_BT709: "bt709", _a
 SITE_NAMES = {_abi.SK_SITE_NONE: "jpeg", _abi.SK_SITE_H_COSITED: "mpeg2"}
 
 
-def default_for_height(out_height: int) -> tuple[int, int]:
+# upstream's set_default_colorimetry() is recalled as switching to bt2020 from 2160
+# lines up.  If real GStreamer caps say otherwise, this is the one name to change (or pass uhd_default).
+UHD_DEFAULT_MATRIX = "bt2020"
+
+
+def default_for_height(out_height: int, uhd_default: str | None = None) -> tuple[int, int]:
     """(matrix, chroma_site) GStreamer assigns to YUV caps that carry neither."""
     if out_height >= 2160:
-        return _abi.SK_MATRIX_BT2020, _abi.SK_SITE_H_COSITED
+        return MATRIX_BY_NAME[uhd_default or UHD_DEFAULT_MATRIX], _abi.SK_SITE_H_COSITED
     if out_height > 576:
         return _abi.SK_MATRIX_BT709, _abi.SK_SITE_H_COSITED
     return _abi.SK_MATRIX_BT601, _abi.SK_SITE_NONE
@@ -67,7 +72,7 @@ def parse_site(chroma_site) -> int | None:
     raise ValueError(f"unsupported chroma-site {chroma_site!r} (none/jpeg, h-cosited/mpeg2)")
 
 
-def resolve(out_height: int, colorimetry=None, chroma_site=None) -> tuple[int, int]:
-    m, s = default_for_height(out_height)
+def resolve(out_height: int, colorimetry=None, chroma_site=None, uhd_default: str | None = None) -> tuple[int, int]:
+    m, s = default_for_height(out_height, uhd_default)
     pm, ps = parse_matrix(colorimetry), parse_site(chroma_site)
     return (m if pm is None else pm, s if ps is None else ps)

@@ -15,7 +15,7 @@ inline int ru(int v, int a) { return (v + a - 1) / a * a; }
 // Integer colour matrix at 8 fractional bits: full-range RGB → limited-range Y'CbCr (scale
 // 219/224/224 over 255), each entry rounded to nearest-even — the derivation GStreamer's converter
 // performs in double before its 8-bit table path.  c[row Y,U,V][col R,G,B].
-inline void matrix_coeffs(int matrix, int c[3][3])
+inline void matrix_coeffs(int matrix, int c[3][3], unsigned switches = 0)
 {
     double kr = 0.299, kb = 0.114;
     if (matrix == SK_MATRIX_BT709) { kr = 0.2126; kb = 0.0722; }
@@ -30,7 +30,7 @@ inline void matrix_coeffs(int matrix, int c[3][3])
         {vr * (1 - kr) * cs, -vr * kg * cs, -vr * kb * cs}};
     for (int i = 0; i < 3; i++)
         for (int j = 0; j < 3; j++)
-            c[i][j] = (int)std::nearbyint(m[i][j]);
+            c[i][j] = (switches & SK_PS_COEFF_HALF_UP) ? (int)std::round(m[i][j]) : (int)std::nearbyint(m[i][j]);
 }
 
 // c = {R, G, B}; byte k of the result multiplies byte k of the pixel word (dp4a operand).
@@ -77,7 +77,7 @@ inline void vertical_taps(int in_size, int out_size, int variant, int32_t *off, 
 // matrix, scale increments).  in_stride and the tiled-kernel fields are the caller's business.
 // Returns the size in bytes of one packed output frame.
 inline size_t fill_geometry(SkGeom &g, int in_w, int in_h, int out_w, int out_h, int in_format, int out_format,
-                            int matrix, int chroma_site, bool damage)
+                            int matrix, int chroma_site, bool damage, unsigned switches = 0)
 {
     g.in_w = in_w;  g.in_h = in_h;  g.out_w = out_w;  g.out_h = out_h;
     const int h2 = ru(out_h, 2);
@@ -97,7 +97,7 @@ inline size_t fill_geometry(SkGeom &g, int in_w, int in_h, int out_w, int out_h,
     g.mb_w = (out_w + 15) / 16;
     g.mb_h = (out_h + 15) / 16;
     int m[3][3];
-    matrix_coeffs(matrix, m);
+    matrix_coeffs(matrix, m, switches);
     g.cy = pack_coeffs(m[0], in_format);
     g.cu = pack_coeffs(m[1], in_format);
     g.cv = pack_coeffs(m[2], in_format);
@@ -106,8 +106,13 @@ inline size_t fill_geometry(SkGeom &g, int in_w, int in_h, int out_w, int out_h,
     g.damage = damage ? 1 : 0;
     g.scale_h = in_w != out_w;
     g.scale_v = in_h != out_h;
-    g.h_inc = out_w > 1 ? (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - 1) : 0;
+    g.h_inc = out_w > 1 ? (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - ((switches & SK_PS_HINC_PLAIN) ? 0 : 1)) : 0;
     g.h_first = ((int64_t)out_w * in_h <= (int64_t)in_w * out_h) ? 1 : 0;
+    if ((switches & SK_PS_V_FIRST_ON_TIE) && (int64_t)out_w * in_h == (int64_t)in_w * out_h) g.h_first = 0;
+    // what the generic kernel has to honour per pixel
+    g.switches = switches & (SK_PS_MATRIX_ROUND | SK_PS_CS_EDGE_KEEP | SK_PS_CHROMA_V_FIRST | SK_PS_CHROMA_BOX4);
+    g.y_off = 4096u + ((switches & SK_PS_MATRIX_ROUND) ? 128u : 0u);
+    g.c_off = 32768u + ((switches & SK_PS_MATRIX_ROUND) ? 128u : 0u);
     return frame_bytes;
 }
 

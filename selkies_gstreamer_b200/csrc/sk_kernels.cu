@@ -13,6 +13,7 @@
 // HBM-bound integer work: no tensor cores on purpose.  Algorithmic traffic is
 // 4 B/px in + 1.5 B/px out + 1.5 B/px previous frame (+1 B per macroblock).
 #include "sk_kernels.h"
+#include "../../include/selkies_preencode.h"     // SK_PS_* switch bits
 
 namespace {
 
@@ -106,6 +107,24 @@ __device__ __forceinline__ void matrix_quad(const uint4 &q, const SkGeom &g, uin
     yw = __byte_perm(t01, t23, 0x5410);
 }
 
+// Same with the accumulator offsets taken from the launch geometry (parity-switch path only: the
+// fast kernels keep them as immediates).
+__device__ __forceinline__ void matrix_quad_sw(const uint4 &q, const SkGeom &g, uint32_t &yw, uint32_t uv[4])
+{
+    const uint32_t p[4] = {q.x, q.y, q.z, q.w};
+    uint32_t ay[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        ay[i] = dp4a_uu(p[i], g.cy, g.y_off);
+        uint32_t au = dp4a_us(p[i], g.cu, (int)g.c_off);
+        uint32_t av = dp4a_us(p[i], g.cv, (int)g.c_off);
+        uv[i] = __byte_perm(au, av, 0x7531);
+    }
+    uint32_t t01 = __byte_perm(ay[0], ay[1], 0x0051);
+    uint32_t t23 = __byte_perm(ay[2], ay[3], 0x0051);
+    yw = __byte_perm(t01, t23, 0x5410);
+}
+
 // Horizontal 4:2:0 filter on 16-bit lanes; x = first pixel of the quad.
 template <int SITE>
 __device__ __forceinline__ void chroma_h(const uint32_t uv[4], uint32_t left, int x, int w,
@@ -121,6 +140,18 @@ __device__ __forceinline__ void chroma_h(const uint32_t uv[4], uint32_t left, in
         uint32_t r1 = (closing && x + 2 == w - 2) ? uv[2] : uv[3];  // [1 3] closing tap (full quad)
         h0 = ((l0 + 2u * uv[0] + r0 + 0x00020002u) >> 2) & 0x00ff00ffu;
         h1 = ((uv[1] + 2u * uv[2] + r1 + 0x00020002u) >> 2) & 0x00ff00ffu;
+    }
+}
+
+// Parity-switch variant: SK_PS_CS_EDGE_KEEP leaves the first and the last chroma sample of a row unfiltered.
+template <int SITE>
+__device__ __forceinline__ void chroma_h_sw(const uint32_t uv[4], uint32_t left, int x, int w, bool keep_edges,
+                                            uint32_t &h0, uint32_t &h1)
+{
+    chroma_h<SITE>(uv, left, x, w, h0, h1);
+    if (SITE == 1 && keep_edges) {
+        if (x == 0 || x == w - 2) h0 = uv[0];
+        if (x + 2 == w - 2) h1 = uv[2];
     }
 }
 
@@ -198,6 +229,12 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// 2-D tiled tensor-map copy global -> shared (c0 = element column, c1 = row), completion on an mbarrier
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
@@ -580,7 +617,9 @@ __device__ __forceinline__ uint32_t sample_px(const uint8_t *in, const SkGeom &g
     return lerp_h(lerp_v(a0, b0, p), lerp_v(a1, b1, p), fr);
 }
 
-template <int FMT, int SITE, bool DAMAGE>
+// SW = true: the parity-switch instantiation (g.switches, g.y_off / g.c_off honoured); SW = false: the
+// arithmetic as restated, untouched.
+template <int FMT, int SITE, bool DAMAGE, bool SW = false>
 __global__ void __launch_bounds__(kThreads)
 sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
 {
@@ -598,6 +637,7 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
     if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
 
     uint32_t hh[2][2];
+    uint32_t uvr[2][4] = {}, leftr[2] = {};      // SW only
     uint32_t diff = 0;
 #pragma unroll
     for (int rr = 0; rr < 2; rr++) {
@@ -619,18 +659,27 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
             q.w = sample_px(f.in, g, x + 3, o, o2, p);
         }
         uint32_t yw, uv[4];
-        matrix_quad(q, g, yw, uv);
+        if (SW) matrix_quad_sw(q, g, yw, uv);
+        else matrix_quad(q, g, yw, uv);
         uint32_t left = 0;
         if (SITE == 1) {
             left = __shfl_up_sync(kFull, uv[3], 1);
             if (lane == 0) {
                 uint32_t hp = (bx0 > 0 && rows_valid) ? sample_px(f.in, g, bx0 - 1, o, o2, p) : 0;
-                uint32_t au = dp4a_us(hp, g.cu, 32768);
-                uint32_t av = dp4a_us(hp, g.cv, 32768);
+                uint32_t au = dp4a_us(hp, g.cu, SW ? (int)g.c_off : 32768);
+                uint32_t av = dp4a_us(hp, g.cv, SW ? (int)g.c_off : 32768);
                 left = __byte_perm(au, av, 0x7531);
             }
         }
-        chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
+        if (SW) {
+            // keep the unfiltered samples: the switch paths below combine the two rows differently
+#pragma unroll
+            for (int i = 0; i < 4; i++) uvr[rr][i] = uv[i];
+            leftr[rr] = left;
+            chroma_h_sw<SITE>(uv, left, x, w, (g.switches & SK_PS_CS_EDGE_KEEP) != 0, hh[rr][0], hh[rr][1]);
+        } else {
+            chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
+        }
         store_word(f.out + (size_t)y * g.y_stride + x, yw, nv);
         if (DAMAGE) {
             uint32_t pyw = load_word<0>(f.prev + (size_t)y * g.y_stride + x, have_prev ? nv : 0);
@@ -640,6 +689,23 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
     {
         const int yc = y0 >> 1;
         uint32_t cw = chroma_v<FMT>(hh[0][0], hh[0][1], hh[1][0], hh[1][1]);
+        if (SW) {
+            constexpr uint32_t kGather = FMT == 0 ? 0x6420 : 0x6240;
+            if (SITE == 0 && (g.switches & SK_PS_CHROMA_BOX4)) {
+                // R4 alternative: the four samples of a 2x2 quad in one rounding
+                const uint32_t b0 = ((uvr[0][0] + uvr[0][1] + uvr[1][0] + uvr[1][1] + 0x00020002u) >> 2) & 0x00ff00ffu;
+                const uint32_t b1 = ((uvr[0][2] + uvr[0][3] + uvr[1][2] + uvr[1][3] + 0x00020002u) >> 2) & 0x00ff00ffu;
+                cw = __byte_perm(b0, b1, kGather);
+            } else if (g.switches & SK_PS_CHROMA_V_FIRST) {
+                // R4 alternative: average the two rows first, filter horizontally second
+                uint32_t va[4], h0, h1;
+#pragma unroll
+                for (int i = 0; i < 4; i++) va[i] = ((uvr[0][i] + uvr[1][i] + 0x00010001u) >> 1) & 0x00ff00ffu;
+                const uint32_t vl = ((leftr[0] + leftr[1] + 0x00010001u) >> 1) & 0x00ff00ffu;
+                chroma_h_sw<SITE>(va, vl, x, w, (g.switches & SK_PS_CS_EDGE_KEEP) != 0, h0, h1);
+                cw = __byte_perm(h0, h1, kGather);
+            }
+        }
         if (FMT == 0) {
             store_word(f.out + g.off_c0 + (size_t)yc * g.c_stride + x, cw, nv);
             if (DAMAGE) {
@@ -705,24 +771,11 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
 //      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
 constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
 
-__device__ __forceinline__ void cp_async16(uint32_t smem_addr, const void *g)
-{
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr), "l"(g) : "memory");
-}
-__device__ __forceinline__ void cp_async8(uint32_t smem_addr, const void *g)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_addr), "l"(g) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit_wait()
-{
-    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
-}
-
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
                                            const int bx0, const int by0, const int lane, const int warp,
                                            const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out,
-                                           const uint32_t bar)
+                                           const uint32_t bar, const CUtensorMap *tmap)
 {
     const int w = g.out_w, h = g.out_h;
 
@@ -767,55 +820,25 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
         }
     }
 
-    // ---- stage: the raw source window of this tile, global -> shared with cp.async (no registers,
-    //      so many CTAs per SM keep their copies in flight while others compute).  Warp w takes
-    //      window rows w, w+8, ... (at most RPW of them), lane l the 16-byte chunks l, l+32, l+64.
+    // ---- stage: the raw source window of this tile (rows sy0.., 16-byte aligned columns cx0..) comes
+    //      global -> shared through ONE 2-D tensor-map copy issued by one thread of the CTA
+    //      (cp.async.bulk.tensor.2d, UTMALDG in SASS; completion on the mbarrier).  The box is the
+    //      largest window any tile of this geometry needs; what falls outside the frame arrives as zeros,
+    //      so edge tiles need no special path.  No thread computes a load address.
     const int xo_first = bx0 > 0 ? bx0 - 1 : 0;                       // halo column included
     const int xo_last = FULL ? bx0 + 127 : min(bx0 + 127, w - 1);
-    int xs_first = xo_first, xs_last = xo_last;
-    if (SH) {
-        xs_first = (xo_first * g.h_inc) >> 16;
-        xs_last = ((xo_last * g.h_inc) >> 16) + 1;
-    }
+    int xs_first = xo_first;
+    if (SH) xs_first = (xo_first * g.h_inc) >> 16;
     const int cx0 = xs_first & ~3;                                    // 16-byte aligned start
-    const int nch = ((xs_last - cx0) >> 2) + 1;                       // <= 96 (host-checked)
     const uint32_t RSB = 4u * (uint32_t)g.scale_raw_stride;           // bytes per raw row
-    // Rows whose last chunk would run past the end of the source row (in_w even but not a multiple of
-    // 4, right edge only) keep the per-chunk cp.async path; every other tile lets the TMA engine copy
-    // each window row with ONE cp.async.bulk issued by one lane, completion on an mbarrier.
-    const bool bulk = cx0 + 4 * nch <= g.in_w;            // CTA-uniform
-    if (bulk) {
-        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0;
-        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW);
-        const uint32_t row_bytes = 16u * (uint32_t)nch;
-        if (warp == 0 && lane == 0) mbar_expect_tx(bar, row_bytes * (uint32_t)nr);
-        if (lane < RPW) {                                  // lane i of warp w copies window row w + 8*i
-            const int r = warp + 8 * lane;
-            if (r < nr) bulk_g2s(raw_s + (uint32_t)r * RSB, base + (size_t)r * (size_t)g.in_stride, row_bytes, bar);
-        }
-        mbar_wait(bar, 0);
-    } else {
-        const uint8_t *base = f.in + (size_t)sy0 * (size_t)g.in_stride + 4 * (size_t)cx0 + 16 * lane;
-        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + 16u * (uint32_t)lane;
-        const int rem_px = g.in_w - cx0 - 4 * lane;      // pixels from this lane's first chunk to the row end
-#pragma unroll
-        for (int i = 0; i < RPW; i++) {
-            const int r = warp + 8 * i;
-            if (r < nr) {                                 // warp-uniform
-                const uint8_t *row = base + (size_t)r * (size_t)g.in_stride;
-                const uint32_t dst = raw_s + (uint32_t)r * RSB;
-#pragma unroll
-                for (int j = 0; j < 3; j++) {
-                    if (lane + 32 * j < nch) {
-                        if (rem_px - 128 * j >= 4) cp_async16(dst + 512 * j, row + 512 * j);
-                        else cp_async8(dst + 512 * j, row + 512 * j);
-                    }
-                }
-            }
-        }
-        cp_async_commit_wait();
-        __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(bar, RSB * (uint32_t)g.scale_rows);
+        tma_load_2d((uint32_t)__cvta_generic_to_shared(RAW), tmap, cx0 >> 1, sy0, bar);
     }
+    // One warp polls the mbarrier; the other seven sleep at the CTA barrier instead of spending issue
+    // slots on try_wait loops (this kernel is issue-bound, not HBM-bound).
+    if (warp == 0) mbar_wait(bar, 0);
+    __syncthreads();
 
     // ---- pass A: h-scale (or copy) the window once into the second shared buffer; lanes own
     //      adjacent output columns, so the gathers are (nearly) bank-conflict free
@@ -833,14 +856,23 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 fr[k] = (uint32_t)(acc >> 8) & 0xffu;
             }
         }
-        const bool want_halo = SITE == 1 && lane == 0 && bx0 > 0;
-        uint32_t hrel4 = 4u * (uint32_t)(xo_first - cx0), hf = 0;
-        if (SH) {
-            const int32_t acc = xo_first * g.h_inc;
-            hrel4 = 4u * (uint32_t)((acc >> 16) - cx0);
-            hf = (uint32_t)(acc >> 8) & 0xffu;
-        }
         const uint8_t *rawb = reinterpret_cast<const uint8_t *>(RAW);
+        // The halo column (output pixel bx0-1, needed by the cosited chroma filter of the tile's first
+        // quad): ONE warp h-scales it for every window row, lane = row, instead of every warp spending
+        // a one-lane instruction stream per row on it.  Warp 7 owns the fewest window rows.
+        if (SITE == 1 && bx0 > 0 && warp == 7) {
+            uint32_t hrel4 = 4u * (uint32_t)(xo_first - cx0), hf = 0;
+            if (SH) {
+                const int32_t acc = xo_first * g.h_inc;
+                hrel4 = 4u * (uint32_t)((acc >> 16) - cx0);
+                hf = (uint32_t)(acc >> 8) & 0xffu;
+            }
+            for (int r = lane; r < nr; r += 32) {
+                const uint8_t *R = rawb + (uint32_t)r * RSB;
+                const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
+                S[r][128] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
+            }
+        }
 #pragma unroll
         for (int i = 0; i < RPW; i++) {
             const int r = warp + 8 * i;
@@ -855,22 +887,34 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 }
 #pragma unroll
                 for (int k = 0; k < 4; k++) Srow[32 * k] = SH ? lerp_h2(a[k], b[k], fr[k]) : a[k];
-                if (want_halo) {
-                    const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
-                    S[r][128] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
-                }
             }
         }
     }
     __syncthreads();
 
     // ---- pass B: vertical 2-tap + matrix + chroma + stores + compare
+    // Chroma of the halo pixel (left neighbour of the warp's first quad, cosited filter only) for both
+    // rows at once: lane r computes row y0+r, lane 0 picks its row's value up with a shuffle below.
+    uint32_t halo_uv = 0;
+    if (SITE == 1 && bx0 > 0 && lane < 2 && (FULL || y0 + lane < h)) {
+        const int yy = y0 + lane;
+        int ra = yy - sy0, rb = ra;
+        uint32_t p = 0;
+        if (SV) {
+            const int o = f.v_off[yy];
+            p = (uint32_t)f.v_tap[yy];
+            ra = o - sy0;
+            rb = min(o + 1, g.in_h - 1) - sy0;
+        }
+        uint32_t hp = S[ra][128];
+        if (SV) hp = lerp_v2(hp, S[rb][128], p);
+        halo_uv = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
+    }
     uint32_t hh[2][2];
 #pragma unroll
     for (int rr = 0; rr < 2; rr++) {
         const int y = y0 + rr;
         uint4 q = make_uint4(0, 0, 0, 0);
-        uint32_t hp = 0;
         if (rows_valid) {
             int ra = y - sy0, rb = ra;
             uint32_t p = 0;
@@ -888,21 +932,14 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 q.z = lerp_v2(q.z, q2.z, p);
                 q.w = lerp_v2(q.w, q2.w, p);
             }
-            if (SITE == 1 && lane == 0) {          // only the warp's first lane needs the halo pixel
-                hp = S[ra][128];
-                if (SV) hp = lerp_v2(hp, S[rb][128], p);
-            }
         }
         uint32_t yw, uv[4];
         matrix_quad(q, g, yw, uv);
         uint32_t left = 0;
         if (SITE == 1) {
             left = __shfl_up_sync(kFull, uv[3], 1);
-            if (lane == 0) {
-                uint32_t au = dp4a_us(hp, g.cu, 32768);
-                uint32_t av = dp4a_us(hp, g.cv, 32768);
-                left = __byte_perm(au, av, 0x7531);
-            }
+            const uint32_t hv = __shfl_sync(kFull, halo_uv, rr);
+            if (lane == 0) left = hv;
         }
         chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
         uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
@@ -934,11 +971,13 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
 // RPW = window rows per warp: 3 (window <= 24 rows, vertical ratio <= 1.375) or 5 (<= 40 rows, ratio <= 2.3)
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW>
 __global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : 3)
-sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch)
+sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch,
+                      const __grid_constant__ SkTmaps maps)
 {
-    extern __shared__ __align__(16) uint32_t sk_smem[];
-    uint32_t (*S)[kScaleRowWords] = reinterpret_cast<uint32_t (*)[kScaleRowWords]>(sk_smem);
-    uint32_t *RAW = sk_smem + (size_t)g.scale_rows * kScaleRowWords;
+    // dynamic shared memory: the raw window first (a TMA destination: 128-byte aligned), then the h-scaled rows
+    extern __shared__ __align__(128) uint32_t sk_smem[];
+    uint32_t *RAW = sk_smem;
+    uint32_t (*S)[kScaleRowWords] = reinterpret_cast<uint32_t (*)[kScaleRowWords]>(sk_smem + (size_t)g.scale_rows * g.scale_raw_stride);
     const SkFrame &f = batch.f[blockIdx.z];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -956,8 +995,9 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     uint32_t diff = 0;
     int nvx = 0;
     bool rows_valid = false;
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar);
+    const CUtensorMap *tmap = &maps.m[blockIdx.z];
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[8];
@@ -1134,11 +1174,11 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
 #endif
 }
 
-cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int /*variant*/)
+cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *maps, int n, cudaStream_t st, int /*variant*/)
 {
     dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
     dim3 block(kThreads);
-    if (g.scale_fast) {
+    if (g.scale_fast && maps != nullptr) {
         const size_t smem = (size_t)g.scale_rows * (kScaleRowWords + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
 #define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
@@ -1147,12 +1187,12 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream
             auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 3>;                             \
             if (smem > 48 * 1024)                                                                     \
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-            kern<<<grid, block, smem, st>>>(g, b);                                                    \
+            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
         } else {                                                                                      \
             auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 5>;                             \
             if (smem > 48 * 1024)                                                                     \
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-            kern<<<grid, block, smem, st>>>(g, b);                                                    \
+            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
         }                                                                                             \
         return cudaGetLastError();                                                                    \
     }
@@ -1163,10 +1203,11 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream
 #undef SK_TILED_MODES
 #undef SK_TILED
     }
-#define SK_CASE(FMT, SITE, DMG)                                                  \
-    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {           \
-        sk_scale_kernel<FMT, SITE, DMG><<<grid, block, 0, st>>>(g, b);           \
-        return cudaGetLastError();                                              \
+#define SK_CASE(FMT, SITE, DMG)                                                              \
+    if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                       \
+        if (g.switches) sk_scale_kernel<FMT, SITE, DMG, true><<<grid, block, 0, st>>>(g, b); \
+        else sk_scale_kernel<FMT, SITE, DMG, false><<<grid, block, 0, st>>>(g, b);           \
+        return cudaGetLastError();                                                          \
     }
     SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
     SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
@@ -1197,7 +1238,7 @@ cudaError_t sk_preload_scale_generic()
     cudaFuncAttributes fa;
     cudaError_t e;
 #define SK_CASE(FMT, SITE, DMG) \
-    if ((e = cudaFuncGetAttributes(&fa, sk_scale_kernel<FMT, SITE, DMG>)) != cudaSuccess) return e;
+    if ((e = cudaFuncGetAttributes(&fa, sk_scale_kernel<FMT, SITE, DMG, false>)) != cudaSuccess) return e;
     SK_CASE(0, 0, true) SK_CASE(0, 1, true) SK_CASE(1, 0, true) SK_CASE(1, 1, true)
     SK_CASE(0, 0, false) SK_CASE(0, 1, false) SK_CASE(1, 0, false) SK_CASE(1, 1, false)
 #undef SK_CASE

@@ -1,6 +1,7 @@
 // sk_kernels.h — internal launch interface between the session runtime and the
 // sm_100a kernels.  Not part of the C ABI.
 #pragma once
+#include <cuda.h>             // CUtensorMap (type only: the driver entry point is looked up at run time)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -28,6 +29,9 @@ struct SkGeom {
     // temporal damage policy (per-macroblock saturating counters updated in the same kernel)
     int pol_threshold, pol_duration, pol_trigger;
     int reverse;              // 1: walk sessions / tiles back to front (alternates per launch, for L2 reuse)
+    // parity switches that change per-pixel arithmetic (SK_PS_*): honoured by the generic kernel only
+    uint32_t switches;
+    uint32_t y_off, c_off;    // matrix accumulator offsets: 4096 / 32768, +128 with SK_PS_MATRIX_ROUND
 };
 
 // Per-session pointers of one launch (all device memory).
@@ -64,6 +68,14 @@ struct SkGather {
 cudaError_t sk_launch_gather(const SkGeom &g, const SkGather &a, cudaStream_t st);
 cudaError_t sk_preload_scale_generic();
 
+// One 2-D tensor map per frame of a launch (tiled scale kernel): the frame's input as
+// [in_h rows][in_w/2 elements of 8 bytes], box = the raw source window of one output tile.  The TMA
+// engine then stages a tile's whole window with ONE instruction (zero-filling what lies outside the frame).
+struct SkTmaps {
+    CUtensorMap m[SK_MAX_BATCH];
+};
+
 // variant: 0 = default. Returns the launch error (no sync).
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);
-cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);
+// maps: one tensor map per frame when g.scale_fast (tiled kernel), else may be nullptr.
+cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *maps, int n, cudaStream_t st, int variant);

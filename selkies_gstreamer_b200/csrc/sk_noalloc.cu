@@ -141,8 +141,9 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
     }
 
     SkGeom g{};
+    if (cfg->parity_switches & ~0x7fu) return fail(errbuf, errbuf_len, SK_ERR_ARG, "unknown parity_switches bit");
     skhost::fill_geometry(g, in_w, in_h, out_w, out_h, cfg->in_format, cfg->out_format, cfg->matrix,
-                          cfg->chroma_site, damage);
+                          cfg->chroma_site, damage, cfg->parity_switches);
     g.in_stride = (int)in_stride;
 
     SkBatch b{};
@@ -156,7 +157,7 @@ extern "C" int sk_scale_frame_noalloc(const sk_config *cfg, const void *d_in, si
     b.f[0].scratch = d_counters;
     b.f[0].v_off = d_off;
     b.f[0].v_tap = d_tap;
-    if ((e = sk_launch_scale(g, b, 1, st, 0)) != cudaSuccess)
+    if ((e = sk_launch_scale(g, b, nullptr, 1, st, 0)) != cudaSuccess)
         return fail(errbuf, errbuf_len, SK_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
     return SK_OK;
 }

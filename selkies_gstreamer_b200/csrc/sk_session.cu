@@ -14,6 +14,8 @@
 #include "sk_kernels.h"
 #include "sk_host_math.h"
 
+#include <cudaTypedefs.h>     // PFN_cuTensorMapEncodeTiled: looked up through the runtime, libcuda is not linked
+
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -23,7 +25,7 @@
 #include <string>
 #include <vector>
 
-static_assert(sizeof(sk_result) == 144 && sizeof(sk_config) == 72, "ABI structs changed: bump SK_ABI_VERSION and the bindings");
+static_assert(sizeof(sk_result) == 144 && sizeof(sk_config) == 76, "ABI structs changed: bump SK_ABI_VERSION and the bindings");
 
 namespace {
 
@@ -49,6 +51,13 @@ struct Slot {          // one staging slot (caller-chosen index)
     cudaEvent_t consumed = nullptr;   // recorded after the kernel that read d_in
     bool consumed_valid = false;
 };
+
+struct TmapSlot {      // a cached 2-D tensor map of one input frame address (tiled scale kernel)
+    const void *ptr = nullptr;
+    size_t stride = 0;
+    CUtensorMap map;
+};
+constexpr int kTmapCache = 8;
 
 struct Ring {          // one output ring entry (submission order)
     uint8_t *d_out = nullptr;
@@ -86,6 +95,7 @@ struct sk_session {
     int n = 2;
     SkGeom geom{};
     bool scaling = false;
+    bool generic_only = false;    // route every frame through sk_scale_kernel (parity switches)
     size_t in_bytes_host = 0;     // in_stride * in_h
     int d_in_stride = 0;
     size_t frame_bytes = 0;
@@ -102,6 +112,8 @@ struct sk_session {
     uint8_t *h_bmeta[kMaxInflight] = {};
     int32_t *d_voff = nullptr;
     int16_t *d_vtap = nullptr;
+    TmapSlot tmaps[kTmapCache];
+    int tmap_next = 0;
     cudaStream_t s_copy = nullptr, s_comp = nullptr, s_d2h = nullptr;
     cudaEvent_t mark[2]{};
     uint64_t seq = 0;
@@ -181,6 +193,7 @@ int validate(const sk_config &c, std::string &why)
         why = "damage_block_threshold, damage_block_duration and paint_over_trigger_frames must be in [1, 255]";
         return SK_ERR_ARG;
     }
+    if (c.parity_switches & ~0x7fu) { why = "unknown parity_switches bit"; return SK_ERR_ARG; }
     if ((c.flags & SK_FLAG_GATED_READBACK) && (!(c.flags & SK_FLAG_HOST_OUTPUT) || (c.flags & SK_FLAG_NO_DAMAGE))) {
         why = "SK_FLAG_GATED_READBACK needs SK_FLAG_HOST_OUTPUT and the damage map";
         return SK_ERR_ARG;
@@ -238,10 +251,64 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     return ri;
 }
 
-cudaError_t launch(const sk_session *s, const SkGeom &g_in, const SkBatch &b, int n, cudaStream_t st)
+// cuTensorMapEncodeTiled through the runtime's driver entry point lookup (once per process).
+PFN_cuTensorMapEncodeTiled tensor_map_encoder()
 {
+    static PFN_cuTensorMapEncodeTiled fn = []() -> PFN_cuTensorMapEncodeTiled {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return reinterpret_cast<PFN_cuTensorMapEncodeTiled>(p);
+    }();
+    return fn;
+}
+
+// The tensor map the tiled scale kernel stages its source windows with, for the frame at `dptr`:
+// [in_h][in_w/2] elements of 8 bytes (two pixels), rows `stride` bytes apart, box = the widest / tallest
+// window any output tile needs (g.scale_raw_stride words x g.scale_rows).  Encoding is a pure host
+// computation (~1 us); maps are cached per input address since sessions cycle through a few buffers.
+const CUtensorMap *input_tensor_map(sk_session *s, const void *dptr, size_t stride)
+{
+    for (TmapSlot &t : s->tmaps)
+        if (t.ptr == dptr && t.stride == stride) return &t.map;
+    PFN_cuTensorMapEncodeTiled enc = tensor_map_encoder();
+    if (!enc) return nullptr;
+    TmapSlot &t = s->tmaps[s->tmap_next];
+    const cuuint64_t dims[2] = {(cuuint64_t)s->geom.in_w / 2, (cuuint64_t)s->geom.in_h};
+    const cuuint64_t strides[1] = {(cuuint64_t)stride};
+    const cuuint32_t box[2] = {(cuuint32_t)s->geom.scale_raw_stride / 2, (cuuint32_t)s->geom.scale_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    if (enc(&t.map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void *>(dptr), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) {
+        t.ptr = nullptr;
+        return nullptr;
+    }
+    t.ptr = dptr;
+    t.stride = stride;
+    s->tmap_next = (s->tmap_next + 1) % kTmapCache;
+    return &t.map;
+}
+
+// ss[i] / b.f[i].in: the frames of this launch.  in_stride comes from g_in.
+cudaError_t launch(sk_session *const *ss, const SkGeom &g_in, const SkBatch &b, int n, cudaStream_t st)
+{
+    const sk_session *s = ss[0];
     g_launches.fetch_add(1, std::memory_order_relaxed);
-    if (s->scaling) return sk_launch_scale(g_in, b, n, st, g_variant.load());
+    if (s->scaling || s->generic_only) {
+        if (!g_in.scale_fast) return sk_launch_scale(g_in, b, nullptr, n, st, g_variant.load());
+        SkTmaps maps;
+        for (int i = 0; i < n; i++) {
+            const CUtensorMap *m = input_tensor_map(ss[i], b.f[i].in, (size_t)g_in.in_stride);
+            if (!m) return cudaErrorInvalidValue;
+            maps.m[i] = *m;
+        }
+        return sk_launch_scale(g_in, b, &maps, n, st, g_variant.load());
+    }
     SkGeom g = g_in;
     g.reverse = (int)(s->seq & 1) && g_snake.load();     // seq was advanced by stage_frame: alternates per frame
     return sk_launch_convert(g, b, n, st, g_variant.load());
@@ -340,7 +407,8 @@ int submit_common(sk_session *s, const SkGeom &g, const uint8_t *d_in, int slot,
     SkBatch b;
     const int ri = stage_frame(s, d_in, frame_id, b.f[0]);
     if (timing) SK_CUDA(s, cudaEventRecord(r.k_start, s->s_comp));
-    cudaError_t le = launch(s, g, b, 1, s->s_comp);
+    sk_session *one[1] = {s};
+    cudaError_t le = launch(one, g, b, 1, s->s_comp);
     if (le != cudaSuccess) {
         s->prev_ring = -1;          // the ring entry was never written: the next frame has no predecessor
         r.valid = false;
@@ -389,6 +457,7 @@ int validate_batch(sk_session **ss, int n)
             ((a.flags ^ b.flags) & (SK_FLAG_NO_DAMAGE | SK_FLAG_POLICY | SK_FLAG_SCALE_GENERIC)) ||
             a.damage_block_threshold != b.damage_block_threshold || a.damage_block_duration != b.damage_block_duration ||
             a.paint_over_trigger_frames != b.paint_over_trigger_frames || a.n_inflight != b.n_inflight ||
+            a.parity_switches != b.parity_switches ||
             s->d_in_stride != L->d_in_stride)
             return fail(L, SK_ERR_STATE, "sessions of one batch must share device and configuration");
         if (s->cfg.flags & SK_FLAG_GATED_READBACK)
@@ -507,6 +576,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     s->dev = c.device_id;
     s->n = c.n_inflight;
     s->scaling = c.in_width != c.out_width || c.in_height != c.out_height;
+    // Per-pixel parity switches are implemented by the generic kernel only (it converts equal sizes too).
+    s->generic_only = (c.parity_switches & (SK_PS_MATRIX_ROUND | SK_PS_CS_EDGE_KEEP | SK_PS_CHROMA_V_FIRST | SK_PS_CHROMA_BOX4)) != 0;
 
 #define SK_TRY(call)                                                                           \
     do {                                                                                       \
@@ -522,7 +593,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
     // geometry (GstVideoInfo default layout)
     SkGeom &g = s->geom;
     s->frame_bytes = skhost::fill_geometry(g, c.in_width, c.in_height, c.out_width, c.out_height, c.in_format,
-                                           c.out_format, c.matrix, c.chroma_site, !(c.flags & SK_FLAG_NO_DAMAGE));
+                                           c.out_format, c.matrix, c.chroma_site, !(c.flags & SK_FLAG_NO_DAMAGE),
+                                           c.parity_switches);
     s->plane_offset[0] = 0;  s->plane_offset[1] = g.off_c0;  s->plane_offset[2] = g.off_c1;
     s->plane_stride[0] = g.y_stride;  s->plane_stride[1] = g.c_stride;
     s->plane_stride[2] = (c.out_format == SK_OUT_I420) ? g.c_stride : 0;
@@ -613,7 +685,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
         g.scale_fast = (order_ok && max_rows <= 40 && max_chunks <= 96 && smem <= 96 * 1024 &&
-                        !(c.flags & SK_FLAG_SCALE_GENERIC)) ? 1 : 0;
+                        !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -806,7 +878,7 @@ int sk_batch_submit(sk_session **ss, int n, const void *const *dptrs, size_t str
     } while (0)
     if (damage) L->bmeta_use[lri]++;
     if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
-    SK_BATCH_CUDA(launch(L, g, b, n, L->s_comp));
+    SK_BATCH_CUDA(launch(ss, g, b, n, L->s_comp));
     SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
     // Read-back of every member rides on the leader's d2h stream; one event closes the batch.
     SK_BATCH_CUDA(cudaStreamWaitEvent(L->s_d2h, lr.k_done, 0));
@@ -865,7 +937,7 @@ int sk_batch_submit_host(sk_session **ss, int n, const void *const *host_in, siz
     }
     Ring &lr = L->ring[ris[0]];
     if (timing) SK_BATCH_CUDA(cudaEventRecord(lr.k_start, L->s_comp));
-    SK_BATCH_CUDA(launch(L, L->geom, b, n, L->s_comp));
+    SK_BATCH_CUDA(launch(ss, L->geom, b, n, L->s_comp));
     SK_BATCH_CUDA(cudaEventRecord(lr.k_done, L->s_comp));
     for (int i = 0; i < n; i++) {
         Slot &sl = ss[i]->slots[slots[i]];

@@ -67,7 +67,7 @@ class PreencodeSession:
                  in_stride: int = 0, damage: bool = True, host_output: bool = True, timing: bool = False,
                  scale_variant: int = _abi.SK_SCALE_VARIANT_GST_LQ, policy: bool = False, damage_block_threshold: int = 0,
                  damage_block_duration: int = 0, paint_over_trigger_frames: int = 0, scale_generic: bool = False,
-                 spin_wait: bool = False, gated_readback: bool = False):
+                 spin_wait: bool = False, gated_readback: bool = False, parity_switches: int = 0):
         self._lib = _abi.load()
         self._h = ctypes.c_void_p()
         if in_format.upper() not in IN_FORMATS:
@@ -88,13 +88,14 @@ class PreencodeSession:
         self.flags = flags
         self.device_index = max(0, int(device_id))
         self.scale_variant = int(scale_variant)
+        self.parity_switches = int(parity_switches)
         self.policy_knobs = (int(damage_block_threshold) or 10, int(damage_block_duration) or 20,
                              int(paint_over_trigger_frames) or 15)
         cfg = _abi.SkConfig(ctypes.sizeof(_abi.SkConfig), device_id, self.width, self.height, self.in_stride,
                             IN_FORMATS[in_format.upper()], self.out_width, self.out_height,
                             OUT_FORMATS[self.out_format], self.matrix, self.site, _abi.SK_SCALE_BILINEAR,
                             scale_variant, n_inflight, flags, damage_block_threshold, damage_block_duration,
-                            paint_over_trigger_frames)
+                            paint_over_trigger_frames, parity_switches)
         rc = self._lib.sk_session_create(ctypes.byref(cfg), ctypes.byref(self._h))
         if rc != _abi.SK_OK:
             self._h = ctypes.c_void_p()

@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_version_and_struct_sizes(lib):
     assert lib.sk_version() == _abi.SK_ABI_VERSION
-    assert ctypes.sizeof(_abi.SkConfig) == 18 * 4
+    assert ctypes.sizeof(_abi.SkConfig) == 19 * 4
     # the header's sk_result: u64, 2 ptr, size_t, 3 size_t, 3 i32 (+pad), 2 ptr, 2 i32, u32, 3 float, 2 ptr, ptr, u64
     # (the library static_asserts the same number)
     assert ctypes.sizeof(_abi.SkResult) == 8 + 16 + 8 + 24 + 16 + 16 + 8 + 4 + 12 + 16 + 8 + 8 == 144
@@ -65,6 +65,7 @@ def test_bad_struct_size_is_rejected(lib):
     (dict(n_inflight=1), _abi.SK_ERR_ARG),
     (dict(in_stride=100), _abi.SK_ERR_ARG),
     (dict(in_width=2, in_height=8192, in_stride=1 << 20), _abi.SK_ERR_ARG),   # 32-bit byte offsets in the kernels
+    (dict(parity_switches=1 << 9), _abi.SK_ERR_ARG),                         # unknown switch bit
     (dict(flags=_abi.SK_FLAG_GATED_READBACK), _abi.SK_ERR_ARG),              # needs SK_FLAG_HOST_OUTPUT
     (dict(flags=_abi.SK_FLAG_GATED_READBACK | _abi.SK_FLAG_HOST_OUTPUT | _abi.SK_FLAG_NO_DAMAGE), _abi.SK_ERR_ARG),
     (dict(out_width=3840, out_height=2160), _abi.SK_ERR_UNSUPPORTED),   # enlarging
