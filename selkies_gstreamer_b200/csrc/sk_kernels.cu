@@ -771,16 +771,21 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
 //      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
 constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
 
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, bool FULL>
+// TR = output rows per CTA tile (16 or 32): a 32-row tile runs pass B twice on one staged window, which
+// halves the per-thread fixed cost (geometry, staging wait, damage tail) per pixel and shrinks the window
+// overlap (44 instead of 2 x 23 source rows at 4:3).
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
                                            const int bx0, const int by0, const int lane, const int warp,
-                                           const bool have_prev, uint32_t &diff, int &nvx_out, bool &rows_valid_out,
+                                           const bool have_prev, uint32_t (&diff)[TR / 16], int &nvx_out,
+                                           bool (&rows_valid_out)[TR / 16],
                                            const uint32_t bar, const CUtensorMap *tmap)
 {
+    constexpr int NG = TR / 16;          // 16-row groups (= macroblock rows) per tile
     const int w = g.out_w, h = g.out_h;
 
     // source-row window of this tile
-    const int ylast = FULL ? by0 + 15 : min(by0 + 15, h - 1);
+    const int ylast = FULL ? by0 + TR - 1 : min(by0 + TR - 1, h - 1);
     int sy0 = by0, sy1 = ylast;
     if (SV) {
         sy0 = f.v_off[by0];
@@ -790,32 +795,46 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
 
     // Previous-frame words of pass B do not depend on shared memory: fetch them first so their
     // latency hides behind pass A.
-    const int y0 = by0 + 2 * warp;
     const int x = bx0 + lane * 4;
     const int nvx = FULL ? 4 : ((w - x) >= 4 ? 4 : ((w - x) > 0 ? 2 : 0));
-    const bool rows_valid = FULL || y0 < h;
-    const int nv = rows_valid ? nvx : 0;
     nvx_out = nvx;
-    rows_valid_out = rows_valid;
-    const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
-    const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
-    uint32_t pyw[2] = {0, 0}, pcw = 0;
-    if (DAMAGE && have_prev) {
-        if (FULL) {
-            pyw[0] = ld4<0>(f.prev + y_off);
-            pyw[1] = ld4<0>(f.prev + y_off + g.y_stride);
-            if (FMT == 0) pcw = ld4<0>(f.prev + g.off_c0 + c_off);
-            else pcw = ld2<0>(f.prev + g.off_c0 + c_off) | (ld2<0>(f.prev + g.off_c1 + c_off) << 16);
-        } else {
-            pyw[0] = load_word<0>(f.prev + y_off, nv);
-            pyw[1] = load_word<0>(f.prev + y_off + g.y_stride, nv);
-            if (FMT == 0) {
-                pcw = load_word<0>(f.prev + g.off_c0 + c_off, nv);
+    uint32_t pyw[NG][2], pcw[NG];
+    int vo[NG][2];
+    uint32_t vt[NG][2];
+#pragma unroll
+    for (int gi = 0; gi < NG; gi++) {
+        const int y0 = by0 + 16 * gi + 2 * warp;
+        const bool rows_valid = FULL || y0 < h;
+        const int nv = rows_valid ? nvx : 0;
+        rows_valid_out[gi] = rows_valid;
+        diff[gi] = 0;
+        const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
+        const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
+        pyw[gi][0] = pyw[gi][1] = pcw[gi] = 0;
+        // vertical taps of this thread's two rows: fetched now, used after the staging wait
+        vo[gi][0] = vo[gi][1] = 0;
+        vt[gi][0] = vt[gi][1] = 0;
+        if (SV && rows_valid) {
+            vo[gi][0] = f.v_off[y0];      vt[gi][0] = (uint32_t)f.v_tap[y0];
+            vo[gi][1] = f.v_off[y0 + 1];  vt[gi][1] = (uint32_t)f.v_tap[y0 + 1];
+        }
+        if (DAMAGE && have_prev) {
+            if (FULL) {
+                pyw[gi][0] = ld4<0>(f.prev + y_off);
+                pyw[gi][1] = ld4<0>(f.prev + y_off + g.y_stride);
+                if (FMT == 0) pcw[gi] = ld4<0>(f.prev + g.off_c0 + c_off);
+                else pcw[gi] = ld2<0>(f.prev + g.off_c0 + c_off) | (ld2<0>(f.prev + g.off_c1 + c_off) << 16);
             } else {
-                uint32_t a = 0, b = 0;
-                if (nv == 4) { a = ld2<0>(f.prev + g.off_c0 + c_off); b = ld2<0>(f.prev + g.off_c1 + c_off); }
-                else if (nv == 2) { a = ld1(f.prev + g.off_c0 + c_off); b = ld1(f.prev + g.off_c1 + c_off); }
-                pcw = a | (b << 16);
+                pyw[gi][0] = load_word<0>(f.prev + y_off, nv);
+                pyw[gi][1] = load_word<0>(f.prev + y_off + g.y_stride, nv);
+                if (FMT == 0) {
+                    pcw[gi] = load_word<0>(f.prev + g.off_c0 + c_off, nv);
+                } else {
+                    uint32_t a = 0, b = 0;
+                    if (nv == 4) { a = ld2<0>(f.prev + g.off_c0 + c_off); b = ld2<0>(f.prev + g.off_c1 + c_off); }
+                    else if (nv == 2) { a = ld1(f.prev + g.off_c0 + c_off); b = ld1(f.prev + g.off_c1 + c_off); }
+                    pcw[gi] = a | (b << 16);
+                }
             }
         }
     }
@@ -892,67 +911,74 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     }
     __syncthreads();
 
-    // ---- pass B: vertical 2-tap + matrix + chroma + stores + compare
-    // Chroma of the halo pixel (left neighbour of the warp's first quad, cosited filter only) for both
-    // rows at once: lane r computes row y0+r, lane 0 picks its row's value up with a shuffle below.
-    uint32_t halo_uv = 0;
-    if (SITE == 1 && bx0 > 0 && lane < 2 && (FULL || y0 + lane < h)) {
-        const int yy = y0 + lane;
-        int ra = yy - sy0, rb = ra;
-        uint32_t p = 0;
-        if (SV) {
-            const int o = f.v_off[yy];
-            p = (uint32_t)f.v_tap[yy];
-            ra = o - sy0;
-            rb = min(o + 1, g.in_h - 1) - sy0;
-        }
-        uint32_t hp = S[ra][128];
-        if (SV) hp = lerp_v2(hp, S[rb][128], p);
-        halo_uv = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
-    }
-    uint32_t hh[2][2];
+    // ---- pass B: vertical 2-tap + matrix + chroma + stores + compare, once per 16-row group
 #pragma unroll
-    for (int rr = 0; rr < 2; rr++) {
-        const int y = y0 + rr;
-        uint4 q = make_uint4(0, 0, 0, 0);
-        if (rows_valid) {
-            int ra = y - sy0, rb = ra;
+    for (int gi = 0; gi < NG; gi++) {
+        const int y0 = by0 + 16 * gi + 2 * warp;
+        const bool rows_valid = FULL || y0 < h;
+        const int nv = rows_valid ? nvx : 0;
+        const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
+        const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
+        // Chroma of the halo pixel (left neighbour of the warp's first quad, cosited filter only) for both
+        // rows at once: lane r computes row y0+r, lane 0 picks its row's value up with a shuffle below.
+        uint32_t halo_uv = 0;
+        if (SITE == 1 && bx0 > 0 && lane < 2 && (FULL || y0 + lane < h)) {
+            const int yy = y0 + lane;
+            int ra = yy - sy0, rb = ra;
             uint32_t p = 0;
             if (SV) {
-                const int o = f.v_off[y];
-                p = (uint32_t)f.v_tap[y];
+                const int o = lane ? vo[gi][1] : vo[gi][0];
+                p = lane ? vt[gi][1] : vt[gi][0];
                 ra = o - sy0;
                 rb = min(o + 1, g.in_h - 1) - sy0;
             }
-            q = *reinterpret_cast<const uint4 *>(&S[ra][4 * lane]);
-            if (SV) {
-                const uint4 q2 = *reinterpret_cast<const uint4 *>(&S[rb][4 * lane]);
-                q.x = lerp_v2(q.x, q2.x, p);
-                q.y = lerp_v2(q.y, q2.y, p);
-                q.z = lerp_v2(q.z, q2.z, p);
-                q.w = lerp_v2(q.w, q2.w, p);
+            uint32_t hp = S[ra][128];
+            if (SV) hp = lerp_v2(hp, S[rb][128], p);
+            halo_uv = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
+        }
+        uint32_t hh[2][2];
+        uint32_t d = 0;
+#pragma unroll
+        for (int rr = 0; rr < 2; rr++) {
+            const int y = y0 + rr;
+            uint4 q = make_uint4(0, 0, 0, 0);
+            if (rows_valid) {
+                int ra = y - sy0, rb = ra;
+                uint32_t p = 0;
+                if (SV) {
+                    const int o = vo[gi][rr];
+                    p = vt[gi][rr];
+                    ra = o - sy0;
+                    rb = min(o + 1, g.in_h - 1) - sy0;
+                }
+                q = *reinterpret_cast<const uint4 *>(&S[ra][4 * lane]);
+                if (SV) {
+                    const uint4 q2 = *reinterpret_cast<const uint4 *>(&S[rb][4 * lane]);
+                    q.x = lerp_v2(q.x, q2.x, p);
+                    q.y = lerp_v2(q.y, q2.y, p);
+                    q.z = lerp_v2(q.z, q2.z, p);
+                    q.w = lerp_v2(q.w, q2.w, p);
+                }
             }
+            uint32_t yw, uv[4];
+            matrix_quad(q, g, yw, uv);
+            uint32_t left = 0;
+            if (SITE == 1) {
+                left = __shfl_up_sync(kFull, uv[3], 1);
+                const uint32_t hv = __shfl_sync(kFull, halo_uv, rr);
+                if (lane == 0) left = hv;
+            }
+            chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
+            uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
+            if (FULL) *reinterpret_cast<uint32_t *>(oy) = yw;
+            else store_word(oy, yw, nv);
+            if (DAMAGE) d |= (yw ^ pyw[gi][rr]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
         }
-        uint32_t yw, uv[4];
-        matrix_quad(q, g, yw, uv);
-        uint32_t left = 0;
-        if (SITE == 1) {
-            left = __shfl_up_sync(kFull, uv[3], 1);
-            const uint32_t hv = __shfl_sync(kFull, halo_uv, rr);
-            if (lane == 0) left = hv;
-        }
-        chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
-        uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
-        if (FULL) *reinterpret_cast<uint32_t *>(oy) = yw;
-        else store_word(oy, yw, nv);
-        if (DAMAGE) diff |= (yw ^ pyw[rr]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
-    }
-    {
         uint32_t cw = chroma_v<FMT>(hh[0][0], hh[0][1], hh[1][0], hh[1][1]);
         if (FMT == 0) {
             if (FULL) *reinterpret_cast<uint32_t *>(f.out + g.off_c0 + c_off) = cw;
             else store_word(f.out + g.off_c0 + c_off, cw, nv);
-            if (DAMAGE) diff |= (cw ^ pcw) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
+            if (DAMAGE) d |= (cw ^ pcw[gi]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x0000ffffu);
         } else {
             uint8_t *pu = f.out + g.off_c0 + c_off;
             uint8_t *pv = f.out + g.off_c1 + c_off;
@@ -963,17 +989,19 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 *pu = (uint8_t)cw;
                 *pv = (uint8_t)(cw >> 16);
             }
-            if (DAMAGE) diff |= (cw ^ pcw) & ((FULL || nvx == 4) ? 0xffffffffu : 0x00ff00ffu);
+            if (DAMAGE) d |= (cw ^ pcw[gi]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x00ff00ffu);
         }
+        diff[gi] = d;
     }
 }
 
-// RPW = window rows per warp: 3 (window <= 24 rows, vertical ratio <= 1.375) or 5 (<= 40 rows, ratio <= 2.3)
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW>
-__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : 3)
+// RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 6: <= 48); TR = output rows per tile.
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR>
+__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? 4 : 3))
 sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch,
                       const __grid_constant__ SkTmaps maps)
 {
+    constexpr int NG = TR / 16;
     // dynamic shared memory: the raw window first (a TMA destination: 128-byte aligned), then the h-scaled rows
     extern __shared__ __align__(128) uint32_t sk_smem[];
     uint32_t *RAW = sk_smem;
@@ -982,44 +1010,49 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int bx0 = blockIdx.x * 128;
-    const int by0 = blockIdx.y * 16;
+    const int by0 = blockIdx.y * TR;
     const bool have_prev = DAMAGE && (f.prev != nullptr);
-    const bool full = (bx0 + 128 <= g.out_w) && (by0 + 16 <= g.out_h);
+    const bool full = (bx0 + 128 <= g.out_w) && (by0 + TR <= g.out_h);
 
     __shared__ __align__(8) unsigned long long s_bar;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) mbar_init(bar, 1);
     if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
     __syncthreads();
-    const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8, blockIdx.x * 8 + threadIdx.x, blockIdx.y) : 0u;
-    uint32_t diff = 0;
+    // thread t < 8*NG publishes macroblock (column t % 8, row t / 8) of this tile
+    const int mb_x = blockIdx.x * 8 + (threadIdx.x & 7), mb_y = blockIdx.y * NG + (threadIdx.x >> 3);
+    const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8 * NG, mb_x, mb_y) : 0u;
+    uint32_t diff[NG];
     int nvx = 0;
-    bool rows_valid = false;
+    bool rows_valid[NG];
     const CUtensorMap *tmap = &maps.m[blockIdx.z];
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
-        __shared__ uint32_t s_mask[8];
-        bool d = rows_valid && nvx > 0 && (diff != 0 || !have_prev);
-        uint32_t m = __ballot_sync(kFull, d);
-        if (lane == 0) s_mask[warp] = m;
+        __shared__ uint32_t s_mask[NG][8];
+#pragma unroll
+        for (int gi = 0; gi < NG; gi++) {
+            const bool d = rows_valid[gi] && nvx > 0 && (diff[gi] != 0 || !have_prev);
+            const uint32_t m = __ballot_sync(kFull, d);
+            if (lane == 0) s_mask[gi][warp] = m;
+        }
         __syncthreads();
         bool hit = false;
-        if (threadIdx.x < 8) {
+        if (threadIdx.x < 8 * NG) {
+            const int gi = threadIdx.x >> 3;
             uint32_t acc = 0;
 #pragma unroll
-            for (int k = 0; k < 8; k++) acc |= s_mask[k];
-            const bool flag = ((acc >> (4 * threadIdx.x)) & 0xfu) != 0;
-            const int bx = blockIdx.x * 8 + threadIdx.x, by = blockIdx.y;
-            if (bx < g.mb_w && by < g.mb_h) {
-                f.map[(size_t)by * g.mb_w + bx] = flag ? 1 : 0;
-                policy_update(f, g, (size_t)by * g.mb_w + bx, flag, pol_state);
+            for (int k = 0; k < 8; k++) acc |= s_mask[gi][k];
+            const bool flag = ((acc >> (4 * (threadIdx.x & 7))) & 0xfu) != 0;
+            if (mb_x < g.mb_w && mb_y < g.mb_h) {
+                f.map[(size_t)mb_y * g.mb_w + mb_x] = flag ? 1 : 0;
+                policy_update(f, g, (size_t)mb_y * g.mb_w + mb_x, flag, pol_state);
                 hit = flag;
             }
         }
         // Block count by the barrier itself, then ONE fire-and-forget atomic (RED) per CTA into a word the
-        // host zeroed before the launch.  (A returning atomic here — the ticket scheme of finish_count —
+        // previous use of the ring entry zeroed.  (A returning atomic here — the ticket scheme of finish_count —
         // kept every CTA's registers allocated ~1 us longer and cost 4.7 % of the kernel rate.)
         const int total = __syncthreads_count(hit);
         if (threadIdx.x == 0 && total != 0 && f.count_out != nullptr) atomicAdd(f.count_out, (uint32_t)total);
@@ -1179,21 +1212,22 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *ma
     dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
     dim3 block(kThreads);
     if (g.scale_fast && maps != nullptr) {
+        const int tr = g.scale_tile_rows;                  // 16 or 32, chosen by the session runtime
+        grid.y = (g.out_h + tr - 1) / tr;
         const size_t smem = (size_t)g.scale_rows * (kScaleRowWords + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
+#define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR)                                              \
+        {                                                                                             \
+            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR>;                       \
+            if (smem > 48 * 1024)                                                                     \
+                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
+            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
+        }
 #define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
         (g.scale_v != 0) == SV) {                                                                     \
-        if (g.scale_rows <= 24) {                                                                     \
-            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 3>;                             \
-            if (smem > 48 * 1024)                                                                     \
-                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
-        } else {                                                                                      \
-            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, 5>;                             \
-            if (smem > 48 * 1024)                                                                     \
-                cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
-        }                                                                                             \
+        if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32)                                  \
+        else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16)                   \
+        else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16)                                           \
         return cudaGetLastError();                                                                    \
     }
 #define SK_TILED_MODES(FMT, SITE, DMG) \
@@ -1202,6 +1236,7 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *ma
         SK_TILED_MODES(0, 0, false) SK_TILED_MODES(0, 1, false) SK_TILED_MODES(1, 0, false) SK_TILED_MODES(1, 1, false)
 #undef SK_TILED_MODES
 #undef SK_TILED
+#undef SK_TILED_LAUNCH
     }
 #define SK_CASE(FMT, SITE, DMG)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                       \

@@ -654,19 +654,22 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         off.resize(g.out_h);
         tap.resize(g.out_h);
         skhost::vertical_taps(g.in_h, g.out_h, c.scale_variant, off.data(), tap.data());
-        // The tiled kernel needs the h pass first (or a single axis) and every 16-row output
-        // tile's source rows inside its shared-memory window (36 rows).
-        int max_rows = 16;
-        if (g.scale_v) {
-            max_rows = 0;
-            for (int by0 = 0; by0 < g.out_h; by0 += 16) {
-                const int ylast = (by0 + 15 < g.out_h) ? by0 + 15 : g.out_h - 1;
+        // The tiled kernel needs the h pass first (or a single axis) and every output tile's source rows
+        // inside its shared-memory window.  Window height for 16-row and for 32-row tiles:
+        auto window_rows = [&](int tr) {
+            if (!g.scale_v) return tr;
+            int most = 0;
+            for (int by0 = 0; by0 < g.out_h; by0 += tr) {
+                const int ylast = (by0 + tr - 1 < g.out_h) ? by0 + tr - 1 : g.out_h - 1;
                 int last = off[ylast] + 1;
                 if (last > g.in_h - 1) last = g.in_h - 1;
                 const int rows = last - off[by0] + 1;
-                if (rows > max_rows) max_rows = rows;
+                if (rows > most) most = rows;
             }
-        }
+            return most;
+        };
+        int max_rows = window_rows(16);
+        const int max_rows32 = window_rows(32);
         // widest raw window (in 16-byte chunks) any 128-column output tile stages
         int max_chunks = 0;
         for (int bx0 = 0; bx0 < g.out_w; bx0 += 128) {
@@ -680,11 +683,22 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
             const int chunks = ((xs_last - (xs_first & ~3)) >> 2) + 1;
             if (chunks > max_chunks) max_chunks = chunks;
         }
-        g.scale_rows = max_rows;
         g.scale_raw_stride = 4 * max_chunks;
-        const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
-        g.scale_fast = (order_ok && max_rows <= 40 && max_chunks <= 96 && smem <= 96 * 1024 &&
+        // 32-row tiles (pass B twice per staged window) when the taller window still lets 4 CTAs share an
+        // SM; SELKIES_PREENCODE_SCALE_TILE=16|32 overrides the choice for A/B runs and tests.
+        const size_t smem32 = (size_t)max_rows32 * (132 + (size_t)g.scale_raw_stride) * 4;
+        bool tile32 = max_rows32 <= 48 && smem32 <= 56 * 1024 && g.out_h >= 64;
+        if (const char *e = std::getenv("SELKIES_PREENCODE_SCALE_TILE")) {
+            if (std::atoi(e) == 16) tile32 = false;
+            else if (std::atoi(e) == 32) tile32 = max_rows32 <= 48 && smem32 <= 96 * 1024;
+        }
+        g.scale_tile_rows = tile32 ? 32 : 16;
+        if (tile32) max_rows = max_rows32;
+        g.scale_rows = max_rows;
+        const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
+        g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
+                        (tile32 || max_rows <= 40) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
