@@ -775,7 +775,7 @@ constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128)
 // halves the per-thread fixed cost (geometry, staging wait, damage tail) per pixel and shrinks the window
 // overlap (44 instead of 2 x 23 source rows at 4:3).
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, bool FULL>
-__device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t (*S)[kScaleRowWords], uint32_t *RAW,
+__device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t *Sb, const int Ss, uint32_t *RAW, uint32_t *HALO,
                                            const int bx0, const int by0, const int lane, const int warp,
                                            const bool have_prev, uint32_t (&diff)[TR / 16], int &nvx_out,
                                            bool (&rows_valid_out)[TR / 16],
@@ -872,7 +872,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             if (SH) {
                 const int32_t acc = xc * g.h_inc;
                 rel4[k] = 4u * (uint32_t)((acc >> 16) - cx0);
-                fr[k] = (uint32_t)(acc >> 8) & 0xffu;
+                const uint32_t fq = (uint32_t)(acc >> 8) & 0xffu;
+                fr[k] = (256u - fq) | (fq << 16);          // the dp2a weight pair, built once per column
             }
         }
         const uint8_t *rawb = reinterpret_cast<const uint8_t *>(RAW);
@@ -889,7 +890,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             for (int r = lane; r < nr; r += 32) {
                 const uint8_t *R = rawb + (uint32_t)r * RSB;
                 const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
-                S[r][128] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
+                HALO[r] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
             }
         }
 #pragma unroll
@@ -897,15 +898,18 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             const int r = warp + 8 * i;
             if (r < nr) {                                 // warp-uniform
                 const uint8_t *R = rawb + (uint32_t)r * RSB;
-                uint32_t *Srow = &S[r][lane];
+                uint32_t *Srow = Sb + r * Ss + lane;
                 uint32_t a[4], b[4];
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
                     a[k] = *reinterpret_cast<const uint32_t *>(R + rel4[k]);
                     b[k] = SH ? *reinterpret_cast<const uint32_t *>(R + rel4[k] + 4) : 0u;
                 }
+                // in-place mode: the row's results overwrite the raw row they were read from, so every
+                // lane's reads of this row must precede any lane's writes
+                __syncwarp();
 #pragma unroll
-                for (int k = 0; k < 4; k++) Srow[32 * k] = SH ? lerp_h2(a[k], b[k], fr[k]) : a[k];
+                for (int k = 0; k < 4; k++) Srow[32 * k] = SH ? blend2(a[k], b[k], fr[k], 0u) : a[k];
             }
         }
     }
@@ -932,8 +936,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 ra = o - sy0;
                 rb = min(o + 1, g.in_h - 1) - sy0;
             }
-            uint32_t hp = S[ra][128];
-            if (SV) hp = lerp_v2(hp, S[rb][128], p);
+            uint32_t hp = HALO[ra];
+            if (SV) hp = lerp_v2(hp, HALO[rb], p);
             halo_uv = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
         }
         uint32_t hh[2][2];
@@ -951,9 +955,9 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                     ra = o - sy0;
                     rb = min(o + 1, g.in_h - 1) - sy0;
                 }
-                q = *reinterpret_cast<const uint4 *>(&S[ra][4 * lane]);
+                q = *reinterpret_cast<const uint4 *>(Sb + ra * Ss + 4 * lane);
                 if (SV) {
-                    const uint4 q2 = *reinterpret_cast<const uint4 *>(&S[rb][4 * lane]);
+                    const uint4 q2 = *reinterpret_cast<const uint4 *>(Sb + rb * Ss + 4 * lane);
                     q.x = lerp_v2(q.x, q2.x, p);
                     q.y = lerp_v2(q.y, q2.y, p);
                     q.z = lerp_v2(q.z, q2.z, p);
@@ -997,7 +1001,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
 
 // RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 6: <= 48); TR = output rows per tile.
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR>
-__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? 4 : 3))
+__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? 5 : 3))
 sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch,
                       const __grid_constant__ SkTmaps maps)
 {
@@ -1005,7 +1009,12 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     // dynamic shared memory: the raw window first (a TMA destination: 128-byte aligned), then the h-scaled rows
     extern __shared__ __align__(128) uint32_t sk_smem[];
     uint32_t *RAW = sk_smem;
-    uint32_t (*S)[kScaleRowWords] = reinterpret_cast<uint32_t (*)[kScaleRowWords]>(sk_smem + (size_t)g.scale_rows * g.scale_raw_stride);
+    // The h-scaled rows live in their own buffer behind the window — or, when a raw row is long enough
+    // (g.scale_inplace), IN the raw row they came from, 8 words in (the halo column's sources are the first
+    // pixels of the raw row and stay intact): half the shared memory, more CTAs per SM.
+    uint32_t *Sb = g.scale_inplace ? RAW + 8 : sk_smem + (size_t)g.scale_rows * g.scale_raw_stride;
+    const int Ss = g.scale_inplace ? g.scale_raw_stride : kScaleRowWords;
+    __shared__ uint32_t s_halo[48];        // h-scaled halo column (output pixel bx0-1), one entry per window row
     const SkFrame &f = batch.f[blockIdx.z];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -1026,8 +1035,8 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     int nvx = 0;
     bool rows_valid[NG];
     const CUtensorMap *tmap = &maps.m[blockIdx.z];
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, true>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, false>(g, f, S, RAW, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[NG][8];
@@ -1214,7 +1223,7 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *ma
     if (g.scale_fast && maps != nullptr) {
         const int tr = g.scale_tile_rows;                  // 16 or 32, chosen by the session runtime
         grid.y = (g.out_h + tr - 1) / tr;
-        const size_t smem = (size_t)g.scale_rows * (kScaleRowWords + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
+        const size_t smem = (size_t)g.scale_rows * ((g.scale_inplace ? 0 : kScaleRowWords) + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
 #define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR)                                              \
         {                                                                                             \
             auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR>;                       \

@@ -25,6 +25,7 @@ struct SkGeom {
     int scale_h, scale_v;     // which axes actually change size
     int scale_fast;           // 1: the shared-memory tiled kernel applies (set by the session runtime)
     int scale_tile_rows;      // tiled kernel: output rows per CTA tile, 16 or 32
+    int scale_inplace;        // tiled kernel: h-scaled rows overwrite their raw rows (no second shared buffer)
     int scale_rows;           // tiled kernel: most source rows any output tile needs
     int scale_raw_stride;     // tiled kernel: words per staged raw row (widest tile window, 16-byte chunks)
     // temporal damage policy (per-macroblock saturating counters updated in the same kernel)

@@ -687,7 +687,10 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
         // 32-row tiles (pass B twice per staged window) when the taller window still lets 4 CTAs share an
         // SM; SELKIES_PREENCODE_SCALE_TILE=16|32 overrides the choice for A/B runs and tests.
-        const size_t smem32 = (size_t)max_rows32 * (132 + (size_t)g.scale_raw_stride) * 4;
+        // in-place h-scaled rows need 8 + 128 words inside a raw row (sk_kernels.cu), and a horizontal pass
+        g.scale_inplace = (g.scale_h && g.scale_raw_stride >= 140 && !std::getenv("SELKIES_PREENCODE_SCALE_SEPARATE")) ? 1 : 0;
+        const size_t row_words = (g.scale_inplace ? 0 : 132) + (size_t)g.scale_raw_stride;
+        const size_t smem32 = (size_t)max_rows32 * row_words * 4;
         bool tile32 = max_rows32 <= 48 && smem32 <= 56 * 1024 && g.out_h >= 64;
         if (const char *e = std::getenv("SELKIES_PREENCODE_SCALE_TILE")) {
             if (std::atoi(e) == 16) tile32 = false;
@@ -696,7 +699,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         g.scale_tile_rows = tile32 ? 32 : 16;
         if (tile32) max_rows = max_rows32;
         g.scale_rows = max_rows;
-        const size_t smem = (size_t)max_rows * (132 + (size_t)g.scale_raw_stride) * 4;
+        const size_t smem = (size_t)max_rows * row_words * 4;
         g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
                         (tile32 || max_rows <= 40) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
