@@ -41,6 +41,9 @@ SINK_TEMPLATE = ("video/x-raw, format=(string){ BGRx, BGRA, RGBx, RGBA }, "
                  "width=(int)[ 2, 8192 ], height=(int)[ 2, 8192 ], framerate=(fraction)[ 0/1, 2147483647/1 ]")
 SRC_TEMPLATE = ("video/x-raw, format=(string){ NV12, I420 }, "
                 "width=(int)[ 2, 8192 ], height=(int)[ 2, 8192 ], framerate=(fraction)[ 0/1, 2147483647/1 ]")
+# The NVENC branches of the reference ask for this on the stage's src side (gstwebrtc_app.py:281-284, :377-380, :434-437)
+CUDA_FEATURE = "memory:CUDAMemory"
+SRC_TEMPLATE_CUDA = SRC_TEMPLATE.replace("video/x-raw,", f"video/x-raw({CUDA_FEATURE}),", 1)
 
 
 class IntRange(tuple):
@@ -223,6 +226,9 @@ class PreEncodeStage:
         "coalesce": (bool, False, None),             # share launches with the other stages of this process (coalesce.py)
         "coalesce-window-us": (int, 200, lambda v: 0 <= v <= 100000),
         "spin-wait": (bool, False, None),            # busy-poll for completion instead of sleeping
+        # offer video/x-raw(memory:CUDAMemory) on the src pad: the frame stays in HBM for a CUDA consumer (NVENC);
+        # the Gst adaptor switches it on when the GstCuda typelib can be imported
+        "cuda-memory-output": (bool, False, None),
     }
     READ_ONLY = ("frames", "damaged-blocks", "damaged-fraction", "total-blocks")
 
@@ -303,9 +309,10 @@ class PreEncodeStage:
         return self._props[name]
 
     # -- negotiation ----------------------------------------------------------
-    @staticmethod
-    def template(direction: str) -> list[dict]:
-        return parse_caps(SINK_TEMPLATE if direction == SINK else SRC_TEMPLATE)
+    def template(self, direction: str) -> list[dict]:
+        if direction == SINK:
+            return parse_caps(SINK_TEMPLATE)
+        return parse_caps(SRC_TEMPLATE + ("; " + SRC_TEMPLATE_CUDA if self._props["cuda-memory-output"] else ""))
 
     def transform_caps(self, direction: str, caps: list[dict], filter_caps: list[dict] | None = None) -> list[dict]:
         """Caps possible on the OTHER pad given `caps` on the `direction` pad.
@@ -316,10 +323,16 @@ class PreEncodeStage:
         (framerate, pixel-aspect-ratio, ...) is kept."""
         out = []
         other_formats = list(SRC_FORMATS if direction == SINK else SINK_FORMATS)
+        cuda = self._props["cuda-memory-output"]
         for st in caps:
-            if st.get("name") != "video/x-raw" or st.get("features") not in (None, "memory:SystemMemory"):
+            feat = st.get("features")
+            if st.get("name") != "video/x-raw":
                 continue
-            o = {k: v for k, v in st.items() if k not in ("format", "colorimetry", "chroma-site", "width", "height")}
+            # the sink pad takes system memory only; the src pad may also hand out device memory
+            if feat not in (None, "memory:SystemMemory") and not (direction == SRC and cuda and feat == CUDA_FEATURE):
+                continue
+            o = {k: v for k, v in st.items()
+                 if k not in ("format", "colorimetry", "chroma-site", "width", "height", "features")}
             o["format"] = other_formats
             for dim in ("width", "height"):
                 v = st.get(dim, IntRange(MIN_DIM, MAX_DIM))
@@ -330,6 +343,8 @@ class PreEncodeStage:
                 else:
                     o[dim] = IntRange(MIN_DIM, MAX_DIM)
             out.append(o)
+            if direction == SINK and cuda:
+                out.append(dict(o, features=CUDA_FEATURE))
         out = intersect_caps(out, self.template(SRC if direction == SINK else SINK))
         if filter_caps is not None:
             out = intersect_caps(filter_caps, out)
@@ -409,6 +424,9 @@ class PreEncodeStage:
                         all(self._in.get(k) == incaps.get(k) for k in ("format", "width", "height")) and
                         all(self._out.get(k) == outcaps.get(k) for k in
                             ("format", "width", "height", "colorimetry", "chroma-site")))
+                if outcaps.get("features") == CUDA_FEATURE and not self._props["cuda-memory-output"]:
+                    raise StageError("memory:CUDAMemory output was not offered (cuda-memory-output is off)")
+                same = same and (self._out.get("features") == outcaps.get("features"))
                 self._in, self._out = dict(incaps), dict(outcaps)
                 if same:
                     return True          # e.g. framerate-only renegotiation (set_framerate, gstwebrtc_app.py:1264-1266)
@@ -444,6 +462,11 @@ class PreEncodeStage:
     @property
     def session(self) -> PreencodeSession | None:
         return self._session
+
+    @property
+    def device_output(self) -> bool:
+        """True when the negotiated src caps are video/x-raw(memory:CUDAMemory): use transform_device()."""
+        return bool(self._out) and self._out.get("features") == CUDA_FEATURE
 
     def src_caps_fields(self) -> dict:
         """colorimetry / chroma-site actually used (what the src caps should advertise)."""
@@ -486,17 +509,7 @@ class PreEncodeStage:
         # The GPU works; this thread sleeps without holding the lock (properties stay settable).
         try:
             r = co.convert(s, in_ptr, stride, out_ptr) if co is not None else s.wait(fid)
-            self.frames += 1
-            # copies: the session's pinned map buffers are reused n_inflight frames later
-            self.last_damage_map = None if r.damage_map is None else r.damage_map.copy()
-            self.last_policy_map = None if r.policy_map is None else r.policy_map.copy()
-            self.last_damaged = r.damaged_count
-            if r.damage_map is not None:
-                if self.on_damage is not None:
-                    self.on_damage(self, self.last_damage_map, r.damaged_count)
-                self.last_decision = self._policy.decide(self.last_damage_map, self.last_policy_map, r.damaged_count)
-                if self.on_decision is not None:
-                    self.on_decision(self, self.last_decision)
+            self._after_frame(r)
             return FLOW_OK
         except (StageError, PreencodeError) as e:
             self.last_error = str(e)
@@ -505,6 +518,62 @@ class PreEncodeStage:
             with self._lock:
                 self._busy -= 1
                 self._lock.notify_all()
+
+    def _after_frame(self, r):
+        self.frames += 1
+        # copies: the session's pinned map buffers are reused n_inflight frames later
+        self.last_damage_map = None if r.damage_map is None else r.damage_map.copy()
+        self.last_policy_map = None if r.policy_map is None else r.policy_map.copy()
+        self.last_damaged = r.damaged_count
+        if r.damage_map is not None:
+            if self.on_damage is not None:
+                self.on_damage(self, self.last_damage_map, r.damaged_count)
+            self.last_decision = self._policy.decide(self.last_damage_map, self.last_policy_map, r.damaged_count)
+            if self.on_decision is not None:
+                self.on_decision(self, self.last_decision)
+
+    def transform_device(self, in_ptr: int, in_size: int, consumer_stream: int = 0, in_stride: int = 0,
+                         pin: bool | None = None):
+        """One frame whose output STAYS IN HBM (src caps video/x-raw(memory:CUDAMemory), the reference's NVENC
+        branches gstwebrtc_app.py:281-284): H2D from the input buffer, kernel, only the maps come back.
+        Returns (FlowReturn, FrameResult or None); the result carries `dev_frame`, `plane_offset`, `plane_stride`
+        and `frame_id`.  `consumer_stream` (a cudaStream_t, 0 = none) is made to wait for the kernel; call
+        release_device(frame_id, stream) after queueing the consumer's read, or copy the surface before
+        n-inflight more frames are converted."""
+        with self._lock:
+            s = self._session
+            if s is None:
+                self.last_error = "not negotiated"
+                return FLOW_NOT_NEGOTIATED, None
+            try:
+                stride = in_stride or 4 * s.width
+                if in_size < stride * (s.height - 1) + 4 * s.width:
+                    raise StageError(f"input buffer too small: {in_size} bytes")
+                if self._props["pin-buffers"] if pin is None else pin:
+                    self._pins.ensure(in_ptr, in_size)
+                fid = s.submit_io(self.frames % s.n_inflight, in_ptr, stride, None)
+                if consumer_stream:
+                    s.wait_device(fid, consumer_stream)
+                self._busy += 1
+            except (StageError, PreencodeError) as e:
+                self.last_error = str(e)
+                return FLOW_ERROR, None
+        try:
+            r = s.wait(fid)                 # maps and count only: the session has no host output
+            self._after_frame(r)
+            return FLOW_OK, r
+        except (StageError, PreencodeError) as e:
+            self.last_error = str(e)
+            return FLOW_ERROR, None
+        finally:
+            with self._lock:
+                self._busy -= 1
+                self._lock.notify_all()
+
+    def release_device(self, frame_id: int, consumer_stream: int):
+        with self._lock:
+            if self._session is not None:
+                self._session.release_device(frame_id, consumer_stream)
 
     def transform_array(self, frame):
         """numpy convenience around transform(): returns (packed output, damage map, count)."""

@@ -309,3 +309,42 @@ def test_pcie_probe_reports_rates():
     assert up.value > 1.0 and down.value > 1.0
     assert lib.sk_pcie_probe(0, 8 << 20, 4, 0, ctypes.byref(up), ctypes.byref(down)) == 0
     assert up.value > 1.0 and down.value == 0.0
+
+
+def test_stage_with_cuda_memory_caps_keeps_the_frame_on_the_gpu():
+    """src caps video/x-raw(memory:CUDAMemory) (the reference's NVENC branches): the stage converts, only the maps come
+    back, a consumer stream reads the surface in HBM — and it is the oracle's frame."""
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from selkies_gstreamer_b200 import stage as st
+    w, h = 1920, 1080
+    s = st.PreEncodeStage()
+    s.set_property("cuda-memory-output", True)
+    sink = st.parse_caps(f"video/x-raw, format=(string)BGRx, width=(int){w}, height=(int){h}, framerate=(fraction)60/1")
+    other = s.transform_caps(st.SINK, sink, st.parse_caps("video/x-raw(memory:CUDAMemory), format=(string)NV12, colorimetry=(string)bt709, chroma-site=(string)mpeg2"))
+    fixed = s.fixate_caps(st.SINK, sink, other)
+    assert s.start() and s.set_caps(sink[0], fixed), s.last_error
+    assert s.device_output and s.session.flags & _abi.SK_FLAG_HOST_OUTPUT == 0
+    consumer = torch.cuda.Stream()
+    frames = [synth.desktop(w, h, seed=2)]
+    frames.append(synth.mutate(frames[0], 0.03, seed=1, aligned=False))
+    frames.append(synth.mutate(frames[1], 0.03, seed=2, aligned=False))
+    seen, prev = [], None
+    for f in frames:
+        rc, r = s.transform_device(f.ctypes.data, f.nbytes, consumer.cuda_stream, pin=False)
+        assert rc == st.FLOW_OK, s.last_error
+        assert r.frame is None and r.dev_frame and r.readback_bytes == 0
+        with torch.cuda.stream(consumer):
+            dst = torch.empty(s.session.frame_bytes, dtype=torch.uint8, device="cuda")
+            dst.copy_(_device_view(torch, r.dev_frame, s.session.frame_bytes), non_blocking=True)
+        s.release_device(r.frame_id, consumer.cuda_stream)
+        seen.append((dst, s.last_damage_map.copy(), s.last_damaged))
+    consumer.synchronize()
+    for k, (f, (dst, dmap, cnt)) in enumerate(zip(frames, seen)):
+        e = expect(f)
+        assert (dst.cpu().numpy() == e).all(), k
+        em, en = o.damage(w, h, 0, e, prev)
+        assert (dmap == em).all() and cnt == en, k
+        prev = e
+    assert s.stop()

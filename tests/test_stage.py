@@ -323,3 +323,26 @@ def test_gst_adaptor_signals_roi_and_keyframes(monkeypatch):
     el.do_set_property(prop(name="damage-block-threshold"), 4)
     assert el.do_get_property(prop(name="damage-block-threshold")) == 4
     assert el.do_get_property(prop(name="roi-meta")) is False
+
+
+def test_cuda_memory_caps_are_offered_only_when_switched_on():
+    """The NVENC branches ask for video/x-raw(memory:CUDAMemory),format=NV12 behind the stage
+    (gstwebrtc_app.py:281-284): offered on the src pad with cuda-memory-output, refused without."""
+    from selkies_gstreamer_b200 import stage as st
+    sink = st.parse_caps("video/x-raw, format=(string)BGRx, width=(int)1920, height=(int)1080, framerate=(fraction)60/1")
+    want = st.parse_caps("video/x-raw(memory:CUDAMemory), format=(string)NV12")
+    s = st.PreEncodeStage()
+    assert s.transform_caps(st.SINK, sink, want) == []                      # off: nothing to agree on
+    assert not s.set_caps(sink[0], dict(want[0], width=1920, height=1080)) and "CUDAMemory" in s.last_error
+    s.set_property("cuda-memory-output", True)
+    got = s.transform_caps(st.SINK, sink, want)
+    assert len(got) == 1 and got[0]["features"] == "memory:CUDAMemory" and got[0]["format"] == "NV12"
+    fixed = s.fixate_caps(st.SINK, sink, got)
+    assert fixed["features"] == "memory:CUDAMemory" and (fixed["width"], fixed["height"]) == (1920, 1080)
+    both = s.transform_caps(st.SINK, sink)
+    assert [c.get("features") for c in both] == [None, "memory:CUDAMemory"]
+    # upstream direction: device-memory src caps map back to plain system-memory sink caps
+    back = s.transform_caps(st.SRC, [dict(fixed)])
+    assert back and all(c.get("features") is None for c in back) and "BGRx" in back[0]["format"]
+    # the sink pad itself never takes device memory
+    assert s.transform_caps(st.SINK, st.parse_caps("video/x-raw(memory:CUDAMemory), format=(string)BGRx, width=(int)64, height=(int)64")) == []
