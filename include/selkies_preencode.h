@@ -300,7 +300,7 @@ int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_
  * The kernel is the library's generic scale kernel (every output pixel gathers its own taps
  * through L1; equal sizes are allowed and then it simply converts) — NOT the shared-memory tiled
  * kernel a session normally runs, which needs per-session set-up.  Output is bit-identical to a
- * session's; it is about 1.7x slower per frame (profiles/r2_noalloc_timing.md).  Its scratch — the
+ * session's; it is 1.6-2.7x slower per frame (profiles/r2_noalloc_timing.md).  Its scratch — the
  * two reduction words of the damage count and one vertical tap entry per output row — lives in a
  * fixed array inside the library image, about 26 KB on every GPU that loads the library, for the
  * life of the process.  Hence the limit: out_height <= SK_NOALLOC_MAX_OUT_HEIGHT, anything taller
