@@ -278,8 +278,9 @@ int sk_marker_record(sk_session *s, int which);
 int sk_marker_elapsed_us(sk_session *s, float *us);
 
 /* Measurement helper: the bare PCIe rate of this process's GPU `device_id`, with nothing of the
- * session machinery involved — `iters` back-to-back cudaMemcpyAsync of `bytes` between one pinned
- * host buffer and one device buffer, timed with CUDA events.  mode 0: host->device only,
+ * session machinery involved — `iters` back-to-back cudaMemcpyAsync of `bytes` between eight pinned
+ * host buffers used in turn (so the host's cache cannot stand in for its memory) and one device
+ * buffer, timed with CUDA events.  mode 0: host->device only,
  * 1: device->host only, 2: both directions at once on two streams.  The rates (GB/s, 0 when the
  * direction was not exercised) are what the frame path's copies are judged against
  * (north_star: "the H2D copy is reported separately against PCIe bandwidth"; the reference has

@@ -1150,6 +1150,7 @@ int sk_marker_elapsed_us(sk_session *s, float *us)
 int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_gbs, double *d2h_gbs)
 {
     if (bytes == 0 || iters < 1 || mode < 0 || mode > 2) return SK_ERR_ARG;
+    constexpr size_t kRot = 8;
     if (h2d_gbs) *h2d_gbs = 0.0;
     if (d2h_gbs) *d2h_gbs = 0.0;
     if (device_id < 0) device_id = 0;
@@ -1158,8 +1159,10 @@ int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaError_t e = cudaSetDevice(device_id);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) {
-        e = cudaHostAlloc(&h[i], bytes, cudaHostAllocDefault);
-        if (e == cudaSuccess) { std::memset(h[i], 0x5a, bytes); e = cudaMalloc(&d[i], bytes); }
+        // kRot distinct host buffers, used in turn: a single buffer copied over and over can be served from
+        // the host's last-level cache, which flatters the rate real frames (a new buffer each) ever see
+        e = cudaHostAlloc(&h[i], bytes * kRot, cudaHostAllocDefault);
+        if (e == cudaSuccess) { std::memset(h[i], 0x5a, bytes * kRot); e = cudaMalloc(&d[i], bytes); }
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreate(&ev[2 * i]);
         if (e == cudaSuccess) e = cudaEventCreate(&ev[2 * i + 1]);
@@ -1175,8 +1178,10 @@ int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_
         if (up) cudaEventRecord(ev[0], st[0]);
         if (down) cudaEventRecord(ev[2], st[1]);
         for (int k = 0; k < iters && e == cudaSuccess; k++) {
-            if (up) e = cudaMemcpyAsync(d[0], h[0], bytes, cudaMemcpyHostToDevice, st[0]);
-            if (e == cudaSuccess && down) e = cudaMemcpyAsync(h[1], d[1], bytes, cudaMemcpyDeviceToHost, st[1]);
+            const size_t o = ((size_t)k % kRot) * bytes;
+            if (up) e = cudaMemcpyAsync(d[0], static_cast<char *>(h[0]) + o, bytes, cudaMemcpyHostToDevice, st[0]);
+            if (e == cudaSuccess && down)
+                e = cudaMemcpyAsync(static_cast<char *>(h[1]) + o, d[1], bytes, cudaMemcpyDeviceToHost, st[1]);
         }
         if (up) cudaEventRecord(ev[1], st[0]);
         if (down) cudaEventRecord(ev[3], st[1]);
