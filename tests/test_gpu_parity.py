@@ -267,6 +267,22 @@ def test_scale_one_axis_enlarging_with_fewer_pixels(dims, kernel):
                        scale_generic=(kernel == "generic"))
 
 
+@pytest.mark.parametrize("layout", ["tile16", "separate-buffer", "tile16+separate-buffer"])
+@pytest.mark.parametrize("dims", [(2560, 1440, 1920, 1080), (1366, 768, 1280, 720), (258, 130, 130, 66), (640, 360, 320, 360)])
+def test_scale_kernel_layouts_that_the_default_choice_skips(dims, layout, monkeypatch):
+    """The session picks 32-row tiles and in-place h-scaled rows when they fit; the 16-row tiles and the
+    separate shared-memory buffer stay reachable (other geometries use them) and must be just as exact."""
+    if "tile16" in layout:
+        monkeypatch.setenv("SELKIES_PREENCODE_SCALE_TILE", "16")
+    if "separate" in layout:
+        monkeypatch.setenv("SELKIES_PREENCODE_SCALE_SEPARATE", "1")
+    w, h, ow, oh = dims
+    f0 = rand_frame(w, h, w + oh)
+    f1 = synth.mutate(f0, 0.04, seed=5, aligned=False)
+    for out_format, site in (("I420", 1), ("NV12", 0)):
+        check_sequence([f0, f1], w, h, out_w=ow, out_h=oh, out_format=out_format, chroma_site=site)
+
+
 @pytest.mark.parametrize("dims", [(1366, 768, 1280, 720), (258, 130, 130, 66), (2560, 1440, 1278, 720), (514, 96, 258, 90)])
 def test_scale_ragged_edges(dims):
     w, h, ow, oh = dims

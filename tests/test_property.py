@@ -94,3 +94,28 @@ def test_gpu_scale_random_geometry(w, h, fx, fy, var, site, fmt, generic, seed):
             em, en = o.damage(ow, oh, ofmt, e, prev)
             assert (r.damage_map == em).all() and r.damaged_count == en
             prev = e
+
+
+@pytest.mark.gpu
+@settings(max_examples=30, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow, HealthCheck.function_scoped_fixture])
+@given(w=even(2, 700), h=even(2, 200), fmt=st.sampled_from(["NV12", "I420"]), n=st.integers(2, 4), site=st.integers(0, 1),
+       seed=st.integers(0, 2**31 - 1))
+def test_gpu_gated_readback_random_geometry(w, h, fmt, n, site, seed):
+    """Damage-gated read-back: whatever the geometry, ring depth and damage pattern, the persistent host frame
+    equals the oracle's whole frame after every conversion."""
+    from selkies_gstreamer_b200 import PreencodeSession
+    rng = np.random.default_rng(seed)
+    ofmt = {"NV12": 0, "I420": 1}[fmt]
+    cur = rng.integers(0, 256, (h, w, 4), dtype=np.uint8)
+    with PreencodeSession(w, h, out_format=fmt, colorimetry=1, chroma_site=site, n_inflight=n, host_output=True,
+                          gated_readback=True) as s:
+        for k in range(2 * n + 3):
+            if k and rng.random() < 0.8:                      # sometimes nothing changes at all
+                cur = cur.copy()
+                for _ in range(int(rng.integers(1, 4))):
+                    y, x = int(rng.integers(0, h)), int(rng.integers(0, w))
+                    cur[y:y + int(rng.integers(1, 20)), x:x + int(rng.integers(1, 40)), :3] ^= 0x3C
+            r = s.convert(cur, slot=k % n)
+            e = o.convert(cur, out_fmt=ofmt, matrix=1, chroma_site=site)
+            assert (r.frame == e).all(), k
+            assert r.readback_bytes % 384 == 0 and r.readback_bytes <= 384 * r.damage_map.size
