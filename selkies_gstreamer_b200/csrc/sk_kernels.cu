@@ -785,13 +785,19 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     const int w = g.out_w, h = g.out_h;
 
     // source-row window of this tile
+    // f.v_pack[y] = {first source row, dp2a weight pair of the two vertical taps}; the second row is always
+    // first + 1 (vertical_taps clamps first to in_h - 2), and the table is padded to an even length.
+    const uint2 *vp = f.v_pack;
     const int ylast = FULL ? by0 + TR - 1 : min(by0 + TR - 1, h - 1);
     int sy0 = by0, sy1 = ylast;
     if (SV) {
-        sy0 = f.v_off[by0];
-        sy1 = min(f.v_off[ylast] + 1, g.in_h - 1);
+        sy0 = (int)vp[by0].x;
+        sy1 = (int)vp[ylast].x + 1;
     }
     const int nr = sy1 - sy0 + 1;
+    // the warp that owns the halo column (see pass A) needs the vertical taps of output row by0 + lane
+    uint2 hvp = make_uint2(0u, 0u);
+    if (SITE == 1 && SV && bx0 > 0 && warp == 7 && lane < TR) hvp = vp[min(by0 + lane, h - 1)];
 
     // Previous-frame words of pass B do not depend on shared memory: fetch them first so their
     // latency hides behind pass A.
@@ -814,9 +820,10 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
         // vertical taps of this thread's two rows: fetched now, used after the staging wait
         vo[gi][0] = vo[gi][1] = 0;
         vt[gi][0] = vt[gi][1] = 0;
-        if (SV && rows_valid) {
-            vo[gi][0] = f.v_off[y0];      vt[gi][0] = (uint32_t)f.v_tap[y0];
-            vo[gi][1] = f.v_off[y0 + 1];  vt[gi][1] = (uint32_t)f.v_tap[y0 + 1];
+        if (SV && rows_valid) {                 // y0 is even: both rows' entries in one 16-byte load
+            const uint4 t = *reinterpret_cast<const uint4 *>(vp + y0);
+            vo[gi][0] = (int)t.x;  vt[gi][0] = t.y;
+            vo[gi][1] = (int)t.z;  vt[gi][1] = t.w;
         }
         if (DAMAGE && have_prev) {
             if (FULL) {
@@ -892,18 +899,33 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
                 HALO[r] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
             }
+            __syncwarp();
+            // ... and finishes it: lane = output row of the tile, vertical 2-tap + the two chroma dot
+            // products, so that pass B only picks one word up per row.
+            if (lane < TR) {
+                const int ra = SV ? (int)hvp.x - sy0 : min(lane, nr - 1);
+                uint32_t hp = HALO[ra];
+                if (SV) hp = blend2(hp, HALO[ra + 1], hvp.y, 128u);
+                HALO[48 + lane] = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
+            }
         }
+        // per-thread parts of the addresses once; the row part is warp-uniform and rides in a uniform register
+        const uint8_t *src_k[4];
 #pragma unroll
-        for (int i = 0; i < RPW; i++) {
+        for (int k = 0; k < 4; k++) src_k[k] = rawb + rel4[k];
+        uint32_t *dst_lane = Sb + lane;
+        uint32_t row_b = __shfl_sync(kFull, (uint32_t)warp * RSB, 0);
+        uint32_t row_s = __shfl_sync(kFull, (uint32_t)(warp * Ss), 0);
+#pragma unroll
+        for (int i = 0; i < RPW; i++, row_b += 8u * RSB, row_s += 8u * (uint32_t)Ss) {
             const int r = warp + 8 * i;
             if (r < nr) {                                 // warp-uniform
-                const uint8_t *R = rawb + (uint32_t)r * RSB;
-                uint32_t *Srow = Sb + r * Ss + lane;
+                uint32_t *Srow = dst_lane + row_s;
                 uint32_t a[4], b[4];
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    a[k] = *reinterpret_cast<const uint32_t *>(R + rel4[k]);
-                    b[k] = SH ? *reinterpret_cast<const uint32_t *>(R + rel4[k] + 4) : 0u;
+                    a[k] = *reinterpret_cast<const uint32_t *>(src_k[k] + row_b);
+                    b[k] = SH ? *reinterpret_cast<const uint32_t *>(src_k[k] + row_b + 4) : 0u;
                 }
                 // in-place mode: the row's results overwrite the raw row they were read from, so every
                 // lane's reads of this row must precede any lane's writes
@@ -923,23 +945,6 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
         const int nv = rows_valid ? nvx : 0;
         const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
         const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
-        // Chroma of the halo pixel (left neighbour of the warp's first quad, cosited filter only) for both
-        // rows at once: lane r computes row y0+r, lane 0 picks its row's value up with a shuffle below.
-        uint32_t halo_uv = 0;
-        if (SITE == 1 && bx0 > 0 && lane < 2 && (FULL || y0 + lane < h)) {
-            const int yy = y0 + lane;
-            int ra = yy - sy0, rb = ra;
-            uint32_t p = 0;
-            if (SV) {
-                const int o = lane ? vo[gi][1] : vo[gi][0];
-                p = lane ? vt[gi][1] : vt[gi][0];
-                ra = o - sy0;
-                rb = min(o + 1, g.in_h - 1) - sy0;
-            }
-            uint32_t hp = HALO[ra];
-            if (SV) hp = lerp_v2(hp, HALO[rb], p);
-            halo_uv = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
-        }
         uint32_t hh[2][2];
         uint32_t d = 0;
 #pragma unroll
@@ -947,21 +952,16 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             const int y = y0 + rr;
             uint4 q = make_uint4(0, 0, 0, 0);
             if (rows_valid) {
-                int ra = y - sy0, rb = ra;
-                uint32_t p = 0;
+                const int ra = SV ? vo[gi][rr] - sy0 : y - sy0;
+                const uint32_t *Sq = Sb + ra * Ss + 4 * lane;
+                q = *reinterpret_cast<const uint4 *>(Sq);
                 if (SV) {
-                    const int o = vo[gi][rr];
-                    p = vt[gi][rr];
-                    ra = o - sy0;
-                    rb = min(o + 1, g.in_h - 1) - sy0;
-                }
-                q = *reinterpret_cast<const uint4 *>(Sb + ra * Ss + 4 * lane);
-                if (SV) {
-                    const uint4 q2 = *reinterpret_cast<const uint4 *>(Sb + rb * Ss + 4 * lane);
-                    q.x = lerp_v2(q.x, q2.x, p);
-                    q.y = lerp_v2(q.y, q2.y, p);
-                    q.z = lerp_v2(q.z, q2.z, p);
-                    q.w = lerp_v2(q.w, q2.w, p);
+                    const uint4 q2 = *reinterpret_cast<const uint4 *>(Sq + Ss);
+                    const uint32_t wp = vt[gi][rr];
+                    q.x = blend2(q.x, q2.x, wp, 128u);
+                    q.y = blend2(q.y, q2.y, wp, 128u);
+                    q.z = blend2(q.z, q2.z, wp, 128u);
+                    q.w = blend2(q.w, q2.w, wp, 128u);
                 }
             }
             uint32_t yw, uv[4];
@@ -969,8 +969,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             uint32_t left = 0;
             if (SITE == 1) {
                 left = __shfl_up_sync(kFull, uv[3], 1);
-                const uint32_t hv = __shfl_sync(kFull, halo_uv, rr);
-                if (lane == 0) left = hv;
+                if (lane == 0) left = HALO[48 + 16 * gi + 2 * warp + rr];     // unused when bx0 == 0
             }
             chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
             uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
@@ -1014,10 +1013,13 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     // pixels of the raw row and stay intact): half the shared memory, more CTAs per SM.
     uint32_t *Sb = g.scale_inplace ? RAW + 8 : sk_smem + (size_t)g.scale_rows * g.scale_raw_stride;
     const int Ss = g.scale_inplace ? g.scale_raw_stride : kScaleRowWords;
-    __shared__ uint32_t s_halo[48];        // h-scaled halo column (output pixel bx0-1), one entry per window row
+    // h-scaled halo column (output pixel bx0-1), one entry per window row; then its chroma pair per output row
+    __shared__ uint32_t s_halo[48 + 32];
     const SkFrame &f = batch.f[blockIdx.z];
     const int lane = threadIdx.x & 31;
-    const int warp = threadIdx.x >> 5;
+    // the shuffle tells the compiler that the warp index is warp-uniform: row addressing and the row-count
+    // branches of pass A then run on the uniform datapath instead of per lane
+    const int warp = __shfl_sync(kFull, (int)(threadIdx.x >> 5), 0);
     const int bx0 = blockIdx.x * 128;
     const int by0 = blockIdx.y * TR;
     const bool have_prev = DAMAGE && (f.prev != nullptr);

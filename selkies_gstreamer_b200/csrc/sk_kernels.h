@@ -49,6 +49,7 @@ struct SkFrame {
     uint32_t *scratch;        // [0] running count, [1] CTA ticket; both return to 0 at kernel end
     const int32_t *v_off;     // scale: first source row per output row
     const int16_t *v_tap;     // scale: second vertical tap (6-bit) per output row
+    const uint2 *v_pack;      // tiled scale kernel: {v_off, (256-4*tap) | (4*tap)<<16} per output row, even length
     uint32_t *state;          // per-macroblock policy state (streak | hot<<8 | still<<16 | dirty<<24), or nullptr
     uint8_t *policy;          // per-macroblock policy flags of this frame (SK_POLICY_*), or nullptr
 };

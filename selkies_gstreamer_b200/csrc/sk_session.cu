@@ -112,6 +112,7 @@ struct sk_session {
     uint8_t *h_bmeta[kMaxInflight] = {};
     int32_t *d_voff = nullptr;
     int16_t *d_vtap = nullptr;
+    uint2 *d_vpack = nullptr;
     TmapSlot tmaps[kTmapCache];
     int tmap_next = 0;
     cudaStream_t s_copy = nullptr, s_comp = nullptr, s_d2h = nullptr;
@@ -168,6 +169,7 @@ void free_session(sk_session *s)
     }
     if (s->d_voff) cudaFree(s->d_voff);
     if (s->d_vtap) cudaFree(s->d_vtap);
+    if (s->d_vpack) cudaFree(s->d_vpack);
     for (cudaEvent_t e : s->mark) if (e) cudaEventDestroy(e);
     if (s->s_copy) cudaStreamDestroy(s->s_copy);
     if (s->s_comp) cudaStreamDestroy(s->s_comp);
@@ -240,6 +242,7 @@ int stage_frame(sk_session *s, const uint8_t *in, uint64_t frame_id, SkFrame &f)
     f.scratch = nullptr;
     f.v_off = s->d_voff;
     f.v_tap = s->d_vtap;
+    f.v_pack = s->d_vpack;
     r.frame_id = frame_id;
     r.valid = true;
     r.waited = false;
@@ -707,6 +710,18 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
         SK_TRY(cudaMemcpy(s->d_vtap, tap.data(), tap.size() * sizeof(int16_t), cudaMemcpyHostToDevice));
+        if (g.scale_fast && g.scale_v) {
+            // the tiled kernel's copy of the table: row and ready-made dp2a weight pair side by side, padded
+            // to an even length so that rows (y, y+1) always load as one 16-byte word
+            std::vector<uint2> pack(((size_t)g.out_h + 1) & ~(size_t)1);
+            for (size_t j = 0; j < pack.size(); j++) {
+                const size_t k = j < (size_t)g.out_h ? j : (size_t)g.out_h - 1;
+                const uint32_t p4 = 4u * (uint32_t)tap[k];
+                pack[j] = make_uint2((uint32_t)off[k], (256u - p4) | (p4 << 16));
+            }
+            SK_TRY(cudaMalloc((void **)&s->d_vpack, pack.size() * sizeof(uint2)));
+            SK_TRY(cudaMemcpy(s->d_vpack, pack.data(), pack.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+        }
     }
     SK_TRY(cudaDeviceSynchronize());
 #undef SK_TRY
