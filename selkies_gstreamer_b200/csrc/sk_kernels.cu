@@ -246,6 +246,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
     if (!done) __trap();        // never hang the GPU on a protocol error
 }
 
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 // ---- no-scale kernel ----------------------------------------------------------
 // CTA = 8 warps.  A warp covers 128*QX pixels of 2*RP rows; lane l owns the
 // quads at x = bx0 + q*128 + 4*l.  The CTA covers 16*RP rows = RP macroblock
@@ -774,8 +785,12 @@ constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128)
 // TR = output rows per CTA tile (16 or 32): a 32-row tile runs pass B twice on one staged window, which
 // halves the per-thread fixed cost (geometry, staging wait, damage tail) per pixel and shrinks the window
 // overlap (44 instead of 2 x 23 source rows at 4:3).
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, bool FULL>
-__device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t *Sb, const int Ss, uint32_t *RAW, uint32_t *HALO,
+//
+// RS = words per staged raw row when the session rounded the window width up to one of the compiled classes
+// (in-place layout only), 0 = taken from the geometry at run time.  A compile-time row stride turns every
+// row step of pass A into an immediate offset of the LDS / STS instructions.
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool FULL>
+__device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t *Sb, const int Ss_rt, uint32_t *RAW, uint32_t *HALO,
                                            const int bx0, const int by0, const int lane, const int warp,
                                            const bool have_prev, uint32_t (&diff)[TR / 16], int &nvx_out,
                                            bool (&rows_valid_out)[TR / 16],
@@ -804,7 +819,9 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     const int x = bx0 + lane * 4;
     const int nvx = FULL ? 4 : ((w - x) >= 4 ? 4 : ((w - x) > 0 ? 2 : 0));
     nvx_out = nvx;
-    uint32_t pyw[NG][2], pcw[NG];
+    // (I420: the previous U and V half-words stay in separate registers until pass B compares them, so that
+    //  nothing here waits for a global load before the staging copy has been issued)
+    uint32_t pyw[NG][2], pcw[NG], pcv[NG];
     int vo[NG][2];
     uint32_t vt[NG][2];
 #pragma unroll
@@ -816,7 +833,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
         diff[gi] = 0;
         const uint32_t y_off = (uint32_t)y0 * (uint32_t)g.y_stride + (uint32_t)x;
         const uint32_t c_off = (uint32_t)(y0 >> 1) * (uint32_t)g.c_stride + (FMT == 0 ? (uint32_t)x : (uint32_t)(x >> 1));
-        pyw[gi][0] = pyw[gi][1] = pcw[gi] = 0;
+        pyw[gi][0] = pyw[gi][1] = pcw[gi] = pcv[gi] = 0;
         // vertical taps of this thread's two rows: fetched now, used after the staging wait
         vo[gi][0] = vo[gi][1] = 0;
         vt[gi][0] = vt[gi][1] = 0;
@@ -830,7 +847,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 pyw[gi][0] = ld4<0>(f.prev + y_off);
                 pyw[gi][1] = ld4<0>(f.prev + y_off + g.y_stride);
                 if (FMT == 0) pcw[gi] = ld4<0>(f.prev + g.off_c0 + c_off);
-                else pcw[gi] = ld2<0>(f.prev + g.off_c0 + c_off) | (ld2<0>(f.prev + g.off_c1 + c_off) << 16);
+                else { pcw[gi] = ld2<0>(f.prev + g.off_c0 + c_off); pcv[gi] = ld2<0>(f.prev + g.off_c1 + c_off); }
             } else {
                 pyw[gi][0] = load_word<0>(f.prev + y_off, nv);
                 pyw[gi][1] = load_word<0>(f.prev + y_off + g.y_stride, nv);
@@ -840,7 +857,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                     uint32_t a = 0, b = 0;
                     if (nv == 4) { a = ld2<0>(f.prev + g.off_c0 + c_off); b = ld2<0>(f.prev + g.off_c1 + c_off); }
                     else if (nv == 2) { a = ld1(f.prev + g.off_c0 + c_off); b = ld1(f.prev + g.off_c1 + c_off); }
-                    pcw[gi] = a | (b << 16);
+                    pcw[gi] = a;  pcv[gi] = b;
                 }
             }
         }
@@ -856,7 +873,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     int xs_first = xo_first;
     if (SH) xs_first = (xo_first * g.h_inc) >> 16;
     const int cx0 = xs_first & ~3;                                    // 16-byte aligned start
-    const uint32_t RSB = 4u * (uint32_t)g.scale_raw_stride;           // bytes per raw row
+    const uint32_t RSB = 4u * (uint32_t)(RS ? RS : g.scale_raw_stride);   // bytes per raw row
+    const int Ss = RS ? RS : Ss_rt;
     if (threadIdx.x == 0) {
         mbar_expect_tx(bar, RSB * (uint32_t)g.scale_rows);
         tma_load_2d((uint32_t)__cvta_generic_to_shared(RAW), tmap, cx0 >> 1, sy0, bar);
@@ -894,6 +912,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 hrel4 = 4u * (uint32_t)((acc >> 16) - cx0);
                 hf = (uint32_t)(acc >> 8) & 0xffu;
             }
+#pragma unroll 1
             for (int r = lane; r < nr; r += 32) {
                 const uint8_t *R = rawb + (uint32_t)r * RSB;
                 const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
@@ -909,29 +928,38 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 HALO[48 + lane] = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
             }
         }
-        // per-thread parts of the addresses once; the row part is warp-uniform and rides in a uniform register
-        const uint8_t *src_k[4];
+        // Shared-space addresses by hand, one register per column (and one for the stores) that already holds
+        // this warp's first row; the empty asm keeps the compiler from re-deriving them row by row.  With a
+        // compile-time stride (RS) every further row is an immediate offset, otherwise one add per register.
+        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + (uint32_t)warp * RSB;
+        uint32_t ak[4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) src_k[k] = rawb + rel4[k];
-        uint32_t *dst_lane = Sb + lane;
-        uint32_t row_b = __shfl_sync(kFull, (uint32_t)warp * RSB, 0);
-        uint32_t row_s = __shfl_sync(kFull, (uint32_t)(warp * Ss), 0);
+        for (int k = 0; k < 4; k++) {
+            ak[k] = raw_s + rel4[k];
+            asm volatile("" : "+r"(ak[k]));
+        }
+        uint32_t os = (uint32_t)__cvta_generic_to_shared(Sb) + 4u * (uint32_t)(lane + warp * Ss);
+        asm volatile("" : "+r"(os));
 #pragma unroll
-        for (int i = 0; i < RPW; i++, row_b += 8u * RSB, row_s += 8u * (uint32_t)Ss) {
-            const int r = warp + 8 * i;
-            if (r < nr) {                                 // warp-uniform
-                uint32_t *Srow = dst_lane + row_s;
+        for (int i = 0; i < RPW; i++) {
+            const uint32_t ioff = RS ? (uint32_t)i * 8u * 4u * (uint32_t)RS : 0u;      // same stride for loads and stores
+            if (warp + 8 * i < nr) {                      // warp-uniform
                 uint32_t a[4], b[4];
 #pragma unroll
                 for (int k = 0; k < 4; k++) {
-                    a[k] = *reinterpret_cast<const uint32_t *>(src_k[k] + row_b);
-                    b[k] = SH ? *reinterpret_cast<const uint32_t *>(src_k[k] + row_b + 4) : 0u;
+                    a[k] = lds32(ak[k] + ioff);
+                    b[k] = SH ? lds32(ak[k] + ioff + 4u) : 0u;
                 }
                 // in-place mode: the row's results overwrite the raw row they were read from, so every
                 // lane's reads of this row must precede any lane's writes
                 __syncwarp();
 #pragma unroll
-                for (int k = 0; k < 4; k++) Srow[32 * k] = SH ? blend2(a[k], b[k], fr[k], 0u) : a[k];
+                for (int k = 0; k < 4; k++) sts32(os + ioff + 128u * k, SH ? blend2(a[k], b[k], fr[k], 0u) : a[k]);
+            }
+            if (!RS) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) ak[k] += 8u * RSB;
+                os += 32u * (uint32_t)Ss;
             }
         }
     }
@@ -992,15 +1020,18 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 *pu = (uint8_t)cw;
                 *pv = (uint8_t)(cw >> 16);
             }
-            if (DAMAGE) d |= (cw ^ pcw[gi]) & ((FULL || nvx == 4) ? 0xffffffffu : 0x00ff00ffu);
+            if (DAMAGE) d |= (((cw & 0xffffu) ^ pcw[gi]) | ((cw >> 16) ^ pcv[gi])) & ((FULL || nvx == 4) ? 0xffffu : 0x00ffu);
         }
         diff[gi] = d;
     }
 }
 
 // RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 6: <= 48); TR = output rows per tile.
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR>
-__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? 5 : 3))
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS>
+#ifndef SK_SCALE_CTAS32
+#define SK_SCALE_CTAS32 5
+#endif
+__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? SK_SCALE_CTAS32 : 3))
 sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch,
                       const __grid_constant__ SkTmaps maps)
 {
@@ -1011,7 +1042,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     // The h-scaled rows live in their own buffer behind the window — or, when a raw row is long enough
     // (g.scale_inplace), IN the raw row they came from, 8 words in (the halo column's sources are the first
     // pixels of the raw row and stay intact): half the shared memory, more CTAs per SM.
-    uint32_t *Sb = g.scale_inplace ? RAW + 8 : sk_smem + (size_t)g.scale_rows * g.scale_raw_stride;
+    uint32_t *Sb = (RS || g.scale_inplace) ? RAW + 8 : sk_smem + (size_t)g.scale_rows * g.scale_raw_stride;
     const int Ss = g.scale_inplace ? g.scale_raw_stride : kScaleRowWords;
     // h-scaled halo column (output pixel bx0-1), one entry per window row; then its chroma pair per output row
     __shared__ uint32_t s_halo[48 + 32];
@@ -1037,8 +1068,8 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     int nvx = 0;
     bool rows_valid[NG];
     const CUtensorMap *tmap = &maps.m[blockIdx.z];
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[NG][8];
@@ -1226,19 +1257,23 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *ma
         const int tr = g.scale_tile_rows;                  // 16 or 32, chosen by the session runtime
         grid.y = (g.out_h + tr - 1) / tr;
         const size_t smem = (size_t)g.scale_rows * ((g.scale_inplace ? 0 : kScaleRowWords) + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
-#define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR)                                              \
+#define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR, RS)                                          \
         {                                                                                             \
-            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR>;                       \
+            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR, RS>;                   \
             if (smem > 48 * 1024)                                                                     \
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
             kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
         }
+    // compiled row-stride classes (SkGeom::scale_raw_stride was rounded up to one by the session runtime)
+    const int rs = (g.scale_inplace && g.scale_h) ? g.scale_raw_stride : 0;
 #define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
         (g.scale_v != 0) == SV) {                                                                     \
-        if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32)                                  \
-        else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16)                   \
-        else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16)                                           \
+        if (tr == 32 && SH && rs == kScaleStride32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, (SH ? kScaleStride32 : 0)) \
+        else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0)                          \
+        else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0)                \
+        else if (SH && rs == kScaleStride16) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (SH ? kScaleStride16 : 0)) \
+        else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, 0)                                        \
         return cudaGetLastError();                                                                    \
     }
 #define SK_TILED_MODES(FMT, SITE, DMG) \

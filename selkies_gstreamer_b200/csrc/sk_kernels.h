@@ -6,6 +6,10 @@
 #include <stdint.h>
 
 constexpr int SK_MAX_BATCH = 32;
+// Row strides (words) the tiled scale kernel is also compiled for as constants: in-place windows of 32-row
+// tiles up to 192 words (shrink ratios up to ~1.4), of 16-row tiles up to 272 words (ratios up to ~2.05).
+constexpr int kScaleStride32 = 192;
+constexpr int kScaleStride16 = 272;
 
 // Geometry + arithmetic constants shared by every frame of one launch.
 struct SkGeom {

@@ -686,21 +686,31 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
             const int chunks = ((xs_last - (xs_first & ~3)) >> 2) + 1;
             if (chunks > max_chunks) max_chunks = chunks;
         }
-        g.scale_raw_stride = 4 * max_chunks;
+        const int need_stride = 4 * max_chunks;
         const bool order_ok = g.h_first || !(g.scale_h && g.scale_v);
+        // in-place h-scaled rows need 8 + 128 words inside a raw row (sk_kernels.cu), and a horizontal pass
+        g.scale_inplace = (g.scale_h && need_stride >= 140 && !std::getenv("SELKIES_PREENCODE_SCALE_SEPARATE")) ? 1 : 0;
+        // In-place windows are widened to the row stride the kernels were compiled for (kScaleStride32 /
+        // kScaleStride16) when they fit one: the TMA box simply reads a few columns more, and every row step
+        // of the kernel becomes an immediate offset.
+        auto stride_for = [&](bool t32, int rows) {
+            if (!g.scale_inplace) return need_stride;
+            if (t32) return need_stride <= kScaleStride32 ? kScaleStride32 : need_stride;
+            return (rows > 24 && need_stride <= kScaleStride16) ? kScaleStride16 : need_stride;
+        };
         // 32-row tiles (pass B twice per staged window) when the taller window still lets 4 CTAs share an
         // SM; SELKIES_PREENCODE_SCALE_TILE=16|32 overrides the choice for A/B runs and tests.
-        // in-place h-scaled rows need 8 + 128 words inside a raw row (sk_kernels.cu), and a horizontal pass
-        g.scale_inplace = (g.scale_h && g.scale_raw_stride >= 140 && !std::getenv("SELKIES_PREENCODE_SCALE_SEPARATE")) ? 1 : 0;
-        const size_t row_words = (g.scale_inplace ? 0 : 132) + (size_t)g.scale_raw_stride;
-        const size_t smem32 = (size_t)max_rows32 * row_words * 4;
+        const size_t sep_words = g.scale_inplace ? 0 : 132;
+        const size_t smem32 = (size_t)max_rows32 * (sep_words + (size_t)stride_for(true, max_rows32)) * 4;
         bool tile32 = max_rows32 <= 48 && smem32 <= 56 * 1024 && g.out_h >= 64;
         if (const char *e = std::getenv("SELKIES_PREENCODE_SCALE_TILE")) {
             if (std::atoi(e) == 16) tile32 = false;
             else if (std::atoi(e) == 32) tile32 = max_rows32 <= 48 && smem32 <= 96 * 1024;
         }
-        g.scale_tile_rows = tile32 ? 32 : 16;
         if (tile32) max_rows = max_rows32;
+        g.scale_raw_stride = stride_for(tile32, max_rows);
+        const size_t row_words = sep_words + (size_t)g.scale_raw_stride;
+        g.scale_tile_rows = tile32 ? 32 : 16;
         g.scale_rows = max_rows;
         const size_t smem = (size_t)max_rows * row_words * 4;
         g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
