@@ -236,6 +236,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
+// the same box, only as far as L2 (no shared-memory destination, no completion to wait for)
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *map, int c0, int c1)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
     uint32_t done = 0;
@@ -782,6 +788,9 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
 //      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
 constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
 
+// All frames of a launch share the geometry, hence the vertical table: any frame's copy serves.
+__device__ __forceinline__ uint32_t batch_vpack(const SkFrame &f, int y) { return f.v_pack[y].x; }
+
 // TR = output rows per CTA tile (16 or 32): a 32-row tile runs pass B twice on one staged window, which
 // halves the per-thread fixed cost (geometry, staging wait, damage tail) per pixel and shrinks the window
 // overlap (44 instead of 2 x 23 source rows at 4:3).
@@ -792,6 +801,7 @@ constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128)
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t *Sb, const int Ss_rt, uint32_t *RAW, uint32_t *HALO,
                                            const int bx0, const int by0, const int lane, const int warp,
+                                           const int sy0, const int sy1,
                                            const bool have_prev, uint32_t (&diff)[TR / 16], int &nvx_out,
                                            bool (&rows_valid_out)[TR / 16],
                                            const uint32_t bar, const CUtensorMap *tmap)
@@ -803,13 +813,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     // f.v_pack[y] = {first source row, dp2a weight pair of the two vertical taps}; the second row is always
     // first + 1 (vertical_taps clamps first to in_h - 2), and the table is padded to an even length.
     const uint2 *vp = f.v_pack;
-    const int ylast = FULL ? by0 + TR - 1 : min(by0 + TR - 1, h - 1);
-    int sy0 = by0, sy1 = ylast;
-    if (SV) {
-        sy0 = (int)vp[by0].x;
-        sy1 = (int)vp[ylast].x + 1;
-    }
-    const int nr = sy1 - sy0 + 1;
+    const int nr = sy1 - sy0 + 1;           // source-row window [sy0, sy1]: fetched by the caller, first thing
     // the warp that owns the halo column (see pass A) needs the vertical taps of output row by0 + lane
     uint2 hvp = make_uint2(0u, 0u);
     if (SITE == 1 && SV && bx0 > 0 && warp == 7 && lane < TR) hvp = vp[min(by0 + lane, h - 1)];
@@ -878,6 +882,21 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     if (threadIdx.x == 0) {
         mbar_expect_tx(bar, RSB * (uint32_t)g.scale_rows);
         tma_load_2d((uint32_t)__cvta_generic_to_shared(RAW), tmap, cx0 >> 1, sy0, bar);
+        // While this window is on its way: ask for the window of the tile that will take this CTA's place
+        // (g.scale_prefetch = CTAs resident on the whole GPU, tiles are handed out x-fastest, then y, then
+        // frame) to be brought into L2, so that its own staging copy later finds it there instead of in HBM.
+        if (g.scale_prefetch > 0) {
+            const uint32_t per_frame = gridDim.x * gridDim.y;
+            const uint32_t lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z) + (uint32_t)g.scale_prefetch;
+            if (lin < per_frame * gridDim.z) {
+                const uint32_t fz = lin / per_frame, rem = lin - fz * per_frame;
+                const uint32_t ty = rem / gridDim.x, tx = rem - ty * gridDim.x;
+                int px = tx > 0 ? (int)tx * 128 - 1 : 0;
+                if (SH) px = (px * g.h_inc) >> 16;
+                const int py = SV ? (int)batch_vpack(f, (int)ty * TR) : (int)ty * TR;
+                tma_prefetch_2d(tmap + ((int)fz - (int)blockIdx.z), (px & ~3) >> 1, py);
+            }
+        }
     }
     // One warp polls the mbarrier; the other seven sleep at the CTA barrier instead of spending issue
     // slots on try_wait loops (this kernel is issue-bound, not HBM-bound).
@@ -1056,11 +1075,19 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     const bool have_prev = DAMAGE && (f.prev != nullptr);
     const bool full = (bx0 + 128 <= g.out_w) && (by0 + TR <= g.out_h);
 
+    // The tile's source-row window decides where the staging copy starts: these two loads go out before
+    // anything else so that their latency overlaps the set-up below.
+    int sy0 = by0, sy1 = min(by0 + TR - 1, g.out_h - 1);
+    if (SV) {
+        const int ylast = sy1;
+        sy0 = (int)f.v_pack[by0].x;
+        sy1 = (int)f.v_pack[ylast].x + 1;
+    }
     __shared__ __align__(8) unsigned long long s_bar;
     const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
     if (threadIdx.x == 0) mbar_init(bar, 1);
     if (DAMAGE && blockIdx.x == 0 && blockIdx.y == 0 && (int)threadIdx.x < f.count_zero_n) f.count_zero[threadIdx.x] = 0u;
-    __syncthreads();
+    if (warp == 0) __syncwarp();        // only warp 0 ever touches the mbarrier: no CTA barrier needed here
     // thread t < 8*NG publishes macroblock (column t % 8, row t / 8) of this tile
     const int mb_x = blockIdx.x * 8 + (threadIdx.x & 7), mb_y = blockIdx.y * NG + (threadIdx.x >> 3);
     const uint32_t pol_state = DAMAGE ? policy_prefetch(f, g, threadIdx.x < 8 * NG, mb_x, mb_y) : 0u;
@@ -1068,8 +1095,8 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     int nvx = 0;
     bool rows_valid[NG];
     const CUtensorMap *tmap = &maps.m[blockIdx.z];
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, have_prev, diff, nvx, rows_valid, bar, tmap);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[NG][8];
@@ -1249,20 +1276,21 @@ cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStre
 #endif
 }
 
-cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *maps, int n, cudaStream_t st, int /*variant*/)
+// One dispatch for both uses of the tiled kernel's template table: launch it (resident == nullptr), or
+// report how many of its CTAs fit one SM for this geometry's shared-memory footprint.
+static cudaError_t tiled_dispatch(const SkGeom &g, const SkBatch *b, const SkTmaps *maps, int n, cudaStream_t st, int *resident)
 {
-    dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
+    const int tr = g.scale_tile_rows;                      // 16 or 32, chosen by the session runtime
+    dim3 grid((g.out_w + 127) / 128, (g.out_h + tr - 1) / tr, n);
     dim3 block(kThreads);
-    if (g.scale_fast && maps != nullptr) {
-        const int tr = g.scale_tile_rows;                  // 16 or 32, chosen by the session runtime
-        grid.y = (g.out_h + tr - 1) / tr;
-        const size_t smem = (size_t)g.scale_rows * ((g.scale_inplace ? 0 : kScaleRowWords) + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
+    const size_t smem = (size_t)g.scale_rows * ((g.scale_inplace ? 0 : kScaleRowWords) + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
 #define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR, RS)                                          \
         {                                                                                             \
             auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR, RS>;                   \
             if (smem > 48 * 1024)                                                                     \
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-            kern<<<grid, block, smem, st>>>(g, b, *maps);                                             \
+            if (resident) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(resident, kern, kThreads, smem); \
+            kern<<<grid, block, smem, st>>>(g, *b, *maps);                                            \
         }
     // compiled row-stride classes (SkGeom::scale_raw_stride was rounded up to one by the session runtime)
     const int rs = (g.scale_inplace && g.scale_h) ? g.scale_raw_stride : 0;
@@ -1273,17 +1301,34 @@ cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *ma
         else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0)                          \
         else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0)                \
         else if (SH && rs == kScaleStride16) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (SH ? kScaleStride16 : 0)) \
+        else if (SH && rs == kScaleStride16n) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (SH ? kScaleStride16n : 0)) \
         else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, 0)                                        \
         return cudaGetLastError();                                                                    \
     }
 #define SK_TILED_MODES(FMT, SITE, DMG) \
     SK_TILED(FMT, SITE, DMG, true, true) SK_TILED(FMT, SITE, DMG, true, false) SK_TILED(FMT, SITE, DMG, false, true)
-        SK_TILED_MODES(0, 0, true) SK_TILED_MODES(0, 1, true) SK_TILED_MODES(1, 0, true) SK_TILED_MODES(1, 1, true)
-        SK_TILED_MODES(0, 0, false) SK_TILED_MODES(0, 1, false) SK_TILED_MODES(1, 0, false) SK_TILED_MODES(1, 1, false)
+    SK_TILED_MODES(0, 0, true) SK_TILED_MODES(0, 1, true) SK_TILED_MODES(1, 0, true) SK_TILED_MODES(1, 1, true)
+    SK_TILED_MODES(0, 0, false) SK_TILED_MODES(0, 1, false) SK_TILED_MODES(1, 0, false) SK_TILED_MODES(1, 1, false)
 #undef SK_TILED_MODES
 #undef SK_TILED
 #undef SK_TILED_LAUNCH
-    }
+    return cudaErrorInvalidValue;
+}
+
+int sk_scale_resident_ctas(const SkGeom &g)
+{
+    if (!g.scale_fast) return 0;
+    int per_sm = 0, dev = 0, sms = 0;
+    if (tiled_dispatch(g, nullptr, nullptr, 1, nullptr, &per_sm) != cudaSuccess) { cudaGetLastError(); return 0; }
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    return per_sm * sms;
+}
+
+cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *maps, int n, cudaStream_t st, int /*variant*/)
+{
+    if (g.scale_fast && maps != nullptr) return tiled_dispatch(g, &b, maps, n, st, nullptr);
+    dim3 grid((g.out_w + 127) / 128, (g.out_h + 15) / 16, n);
+    dim3 block(kThreads);
 #define SK_CASE(FMT, SITE, DMG)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG) {                       \
         if (g.switches) sk_scale_kernel<FMT, SITE, DMG, true><<<grid, block, 0, st>>>(g, b); \

@@ -7,8 +7,9 @@
 
 constexpr int SK_MAX_BATCH = 32;
 // Row strides (words) the tiled scale kernel is also compiled for as constants: in-place windows of 32-row
-// tiles up to 192 words (shrink ratios up to ~1.4), of 16-row tiles up to 272 words (ratios up to ~2.05).
+// tiles up to 192 words (shrink ratios up to ~1.4), of 16-row tiles up to 208 words (3:2) or 272 words (2:1).
 constexpr int kScaleStride32 = 192;
+constexpr int kScaleStride16n = 208;
 constexpr int kScaleStride16 = 272;
 
 // Geometry + arithmetic constants shared by every frame of one launch.
@@ -32,6 +33,7 @@ struct SkGeom {
     int scale_inplace;        // tiled kernel: h-scaled rows overwrite their raw rows (no second shared buffer)
     int scale_rows;           // tiled kernel: most source rows any output tile needs
     int scale_raw_stride;     // tiled kernel: words per staged raw row (widest tile window, 16-byte chunks)
+    int scale_prefetch;       // tiled kernel: CTAs resident on the GPU = how far ahead a CTA asks for a window in L2 (0: off)
     // temporal damage policy (per-macroblock saturating counters updated in the same kernel)
     int pol_threshold, pol_duration, pol_trigger;
     int reverse;              // 1: walk sessions / tiles back to front (alternates per launch, for L2 reuse)
@@ -86,3 +88,6 @@ struct SkTmaps {
 cudaError_t sk_launch_convert(const SkGeom &g, const SkBatch &b, int n, cudaStream_t st, int variant);
 // maps: one tensor map per frame when g.scale_fast (tiled kernel), else may be nullptr.
 cudaError_t sk_launch_scale(const SkGeom &g, const SkBatch &b, const SkTmaps *maps, int n, cudaStream_t st, int variant);
+// CTAs of the tiled scale kernel this geometry selects that are resident on the current device at once
+// (occupancy x SM count); 0 when the tiled kernel does not apply.
+int sk_scale_resident_ctas(const SkGeom &g);

@@ -696,7 +696,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         auto stride_for = [&](bool t32, int rows) {
             if (!g.scale_inplace) return need_stride;
             if (t32) return need_stride <= kScaleStride32 ? kScaleStride32 : need_stride;
-            return (rows > 24 && need_stride <= kScaleStride16) ? kScaleStride16 : need_stride;
+            if (rows <= 24) return need_stride;
+            return need_stride <= kScaleStride16n ? kScaleStride16n : (need_stride <= kScaleStride16 ? kScaleStride16 : need_stride);
         };
         // 32-row tiles (pass B twice per staged window) when the taller window still lets 4 CTAs share an
         // SM; SELKIES_PREENCODE_SCALE_TILE=16|32 overrides the choice for A/B runs and tests.
@@ -716,6 +717,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
                         (tile32 || max_rows <= 40) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
+        // how far ahead a CTA asks for a window to be brought into L2: the CTAs resident on this GPU
+        g.scale_prefetch = std::getenv("SELKIES_PREENCODE_SCALE_NO_PREFETCH") ? 0 : sk_scale_resident_ctas(g);
         SK_TRY(cudaMalloc((void **)&s->d_voff, off.size() * sizeof(int32_t)));
         SK_TRY(cudaMalloc((void **)&s->d_vtap, tap.size() * sizeof(int16_t)));
         SK_TRY(cudaMemcpy(s->d_voff, off.data(), off.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
