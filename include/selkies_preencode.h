@@ -43,7 +43,7 @@ enum {
     SK_ERR_CUDA = -2,         /* CUDA runtime error, incl. "no device"; see sk_last_error()    */
     SK_ERR_ALIGN = -3,        /* device input pointer / stride not 16-byte aligned             */
     SK_ERR_STATE = -4,        /* slot busy, unknown frame id, session mismatch in a batch      */
-    SK_ERR_UNSUPPORTED = -5,  /* e.g. up-scaling (reference never enlarges before the encoder) */
+    SK_ERR_UNSUPPORTED = -5,  /* e.g. a scale_method other than bilinear */
     SK_ERR_NOMEM = -6
 };
 
@@ -110,7 +110,8 @@ typedef struct sk_config {
     int32_t  in_width, in_height;
     int32_t  in_stride;       /* bytes per captured row; 0 = 4*in_width                            */
     int32_t  in_format;       /* SK_IN_*                                                           */
-    int32_t  out_width, out_height;   /* 0 = same as input                                         */
+    int32_t  out_width, out_height;   /* 0 = same as input; smaller or larger (a picture that grows is
+                                         scaled behind the matrix, as upstream's chain_scale() does)  */
     int32_t  out_format;      /* SK_OUT_*                                                          */
     int32_t  matrix;          /* SK_MATRIX_*                                                       */
     int32_t  chroma_site;     /* SK_SITE_*                                                         */
@@ -305,7 +306,8 @@ int sk_pcie_probe(int device_id, size_t bytes, int iters, int mode, double *h2d_
  * two reduction words of the damage count and one vertical tap entry per output row — lives in a
  * fixed array inside the library image, about 26 KB on every GPU that loads the library, for the
  * life of the process.  Hence the limit: out_height <= SK_NOALLOC_MAX_OUT_HEIGHT, anything taller
- * is refused with SK_ERR_ARG and a message in errbuf (use a session for it).
+ * is refused with SK_ERR_ARG and a message in errbuf (use a session for it).  Enlarging (more
+ * output than input pixels) is refused with SK_ERR_UNSUPPORTED here; sessions do it.
  *
  *   cfg        geometry, formats, matrix, chroma_site, scale_variant, SK_FLAG_NO_DAMAGE as
  *              for sk_session_create; device_id < 0 means the calling thread's current

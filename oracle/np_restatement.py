@@ -102,14 +102,19 @@ def convert(frame: np.ndarray, *, in_fmt="BGRx", out_fmt="NV12", matrix="bt709",
     out_w = out_w or w
     out_h = out_h or h
     r, g, b = rgb_planes(frame, in_fmt)
-    if (out_w, out_h) != (w, h):
+    scaling = (out_w, out_h) != (w, h)
+    h_first = out_w * h <= w * out_h
+    if switches & PS_V_FIRST_ON_TIE and out_w * h == w * out_h:
+        h_first = False
+    growing = out_w * out_h > w * h          # then the scaler runs behind the matrix, on Y/U/V
+    if scaling and not growing:
         rgb = np.stack([r, g, b], axis=-1)
-        h_first = out_w * h <= w * out_h
-        if switches & PS_V_FIRST_ON_TIE and out_w * h == w * out_h:
-            h_first = False
         rgb = scale_2tap_lq(rgb, out_w, out_h, v_off, v_tap, h_inc, h_first)
         r, g, b = rgb[..., 0], rgb[..., 1], rgb[..., 2]
     y, u, v = to_yuv444(r, g, b, matrix, switches)
+    if scaling and growing:
+        yuv = scale_2tap_lq(np.stack([y, u, v], axis=-1).astype(np.int64), out_w, out_h, v_off, v_tap, h_inc, h_first)
+        y, u, v = yuv[..., 0], yuv[..., 1], yuv[..., 2]
     assert y.min() >= 0 and y.max() <= 255 and u.min() >= 0 and u.max() <= 255 and v.min() >= 0 and v.max() <= 255
     return (y.astype(np.uint8), chroma_420(u, site, switches).astype(np.uint8), chroma_420(v, site, switches).astype(np.uint8))
 

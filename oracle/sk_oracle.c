@@ -5,8 +5,8 @@
  * 1.24.12 is a non-vendored dependency of the reference; this restates its
  * generic converter chain for BGRx/RGBx -> I420/NV12, 8 bit:
  *
- *     unpack -> [2-tap down-scale] -> 8-bit matrix table -> chroma h/v
- *     down-sample -> pack
+ *     unpack -> [2-tap scale, picture not growing] -> 8-bit matrix table ->
+ *     [2-tap scale, picture growing] -> chroma h/v down-sample -> pack
  *
  * Reference call sites that select this chain (element names only; the
  * reference holds no pixel arithmetic of its own):
@@ -349,7 +349,7 @@ typedef struct {
     const uint8_t *in;
     uint8_t *out;
     matrix_tables tab;
-    int scaling, h_first;
+    int scaling, h_first, scale_after;
     int32_t h_inc;
     int32_t *v_off;
     int16_t *v_tap;
@@ -362,8 +362,21 @@ typedef struct {
     int y0, y1;     /* output line band, y0 even */
 } band;
 
+/* One source line as the scaler sees it: unpacked ARGB when the scaler runs in front of
+ * the matrix (fewer or equal output pixels), already converted AYUV when it runs behind it
+ * (video-converter.c: chain_scale() is called twice, in front of chain_convert() without and
+ * behind it with "force"; the first call only acts when out pixels <= in pixels). */
+static void source_line(const job *j, int row, uint8_t *dst)
+{
+    const sko_config *c = j->cfg;
+    unpack_line(c->in_fmt, j->in + (size_t)row * c->in_stride, dst, c->in_w);
+    if (j->scale_after)
+        matrix8_table(&j->tab, dst, c->in_w);
+}
+
 /* One converted AYUV output line (video-converter.c: the line-cache chain up to
- * and including chain_convert). tmp holds 3 lines of max(in_w,out_w)*4 bytes. */
+ * and including chain_convert, plus the second chain_scale when enlarging). tmp holds 3
+ * lines of max(in_w,out_w)*4 bytes. */
 static void make_ayuv_line(const job *j, int y, uint8_t *dst, uint8_t *tmp)
 {
     const sko_config *c = j->cfg;
@@ -376,11 +389,11 @@ static void make_ayuv_line(const job *j, int y, uint8_t *dst, uint8_t *tmp)
         int16_t p1 = (c->in_h == c->out_h) ? 0 : j->v_tap[y];
         int o2 = (o + 1 < c->in_h) ? o + 1 : o;
         if (j->h_first) {
-            unpack_line(c->in_fmt, j->in + (size_t)o * c->in_stride, u, c->in_w);
+            source_line(j, o, u);
             if (c->in_w != c->out_w) hscale_2tap_lq(u, a, j->h_inc, c->out_w);
             else memcpy(a, u, (size_t)c->in_w * 4);
             if (c->in_h != c->out_h) {
-                unpack_line(c->in_fmt, j->in + (size_t)o2 * c->in_stride, u, c->in_w);
+                source_line(j, o2, u);
                 if (c->in_w != c->out_w) hscale_2tap_lq(u, b, j->h_inc, c->out_w);
                 else memcpy(b, u, (size_t)c->in_w * 4);
                 vscale_2tap_lq(a, b, dst, p1, c->out_w * 4);
@@ -388,9 +401,9 @@ static void make_ayuv_line(const job *j, int y, uint8_t *dst, uint8_t *tmp)
                 memcpy(dst, a, (size_t)c->out_w * 4);
             }
         } else {
-            unpack_line(c->in_fmt, j->in + (size_t)o * c->in_stride, a, c->in_w);
+            source_line(j, o, a);
             if (c->in_h != c->out_h) {
-                unpack_line(c->in_fmt, j->in + (size_t)o2 * c->in_stride, b, c->in_w);
+                source_line(j, o2, b);
                 vscale_2tap_lq(a, b, u, p1, c->in_w * 4);
             } else {
                 memcpy(u, a, (size_t)c->in_w * 4);
@@ -398,6 +411,8 @@ static void make_ayuv_line(const job *j, int y, uint8_t *dst, uint8_t *tmp)
             if (c->in_w != c->out_w) hscale_2tap_lq(u, dst, j->h_inc, c->out_w);
             else memcpy(dst, u, (size_t)c->in_w * 4);
         }
+        if (j->scale_after)
+            return;
     }
     matrix8_table(&j->tab, dst, c->out_w);
 }
@@ -440,7 +455,8 @@ static void *band_main(void *arg)
     job *j = b->j;
     const sko_config *c = j->cfg;
     int wmax = c->in_w > c->out_w ? c->in_w : c->out_w;
-    uint8_t *l0 = (uint8_t *)malloc((size_t)wmax * 4 * 5);
+    /* + one pixel: with SKO_PS_HINC_PLAIN the last h tap pair may start on the last source pixel (weight 0) */
+    uint8_t *l0 = (uint8_t *)calloc((size_t)wmax * 4 * 5 + 16, 1);
     uint8_t *l1 = l0 + (size_t)wmax * 4;
     uint8_t *tmp = l1 + (size_t)wmax * 4;
     int y;
@@ -487,15 +503,15 @@ int sko_convert(const sko_config *cfg, const uint8_t *in, uint8_t *out)
     if (cfg->in_w < 2 || cfg->in_h < 2 || cfg->out_w < 2 || cfg->out_h < 2) return -2;
     if ((cfg->in_w | cfg->in_h | cfg->out_w | cfg->out_h) & 1) return -2;
     if (cfg->in_stride < cfg->in_w * 4) return -3;
-    /* video-converter.c chain_scale(): only the shrinking (or equal) order —
-     * scale before the matrix — is restated. */
-    if ((int64_t)cfg->out_w * cfg->out_h > (int64_t)cfg->in_w * cfg->in_h) return -4;
 
     memset(&j, 0, sizeof j);
     j.cfg = cfg;  j.in = in;  j.out = out;
     init_tables(&j.tab, cfg->matrix, cfg->switches);
     sko_out_layout(cfg->out_w, cfg->out_h, cfg->out_fmt, j.off, j.stride);
     j.scaling = (cfg->in_w != cfg->out_w) || (cfg->in_h != cfg->out_h);
+    /* video-converter.c chain_scale(): in front of the matrix while the picture does not
+     * grow, behind it (on AYUV) when it does. */
+    j.scale_after = (int64_t)cfg->out_w * cfg->out_h > (int64_t)cfg->in_w * cfg->in_h;
     /* chain_scale(): h first when out_w*in_h <= in_w*out_h. */
     j.h_first = ((int64_t)cfg->out_w * cfg->in_h <= (int64_t)cfg->in_w * cfg->out_h);
     if ((cfg->switches & SKO_PS_V_FIRST_ON_TIE) && (int64_t)cfg->out_w * cfg->in_h == (int64_t)cfg->in_w * cfg->out_h)

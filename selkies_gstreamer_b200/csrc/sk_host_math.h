@@ -106,6 +106,8 @@ inline size_t fill_geometry(SkGeom &g, int in_w, int in_h, int out_w, int out_h,
     g.damage = damage ? 1 : 0;
     g.scale_h = in_w != out_w;
     g.scale_v = in_h != out_h;
+    // upstream chain_scale(): in front of the matrix while out pixels <= in pixels, behind it otherwise
+    g.scale_after = ((int64_t)out_w * out_h > (int64_t)in_w * in_h) ? 1 : 0;
     g.h_inc = out_w > 1 ? (int32_t)((((int64_t)in_w - 1) << 16) / (out_w - 1) - ((switches & SK_PS_HINC_PLAIN) ? 0 : 1)) : 0;
     g.h_first = ((int64_t)out_w * in_h <= (int64_t)in_w * out_h) ? 1 : 0;
     if ((switches & SK_PS_V_FIRST_ON_TIE) && (int64_t)out_w * in_h == (int64_t)in_w * out_h) g.h_first = 0;

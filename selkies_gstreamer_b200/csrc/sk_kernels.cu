@@ -610,6 +610,22 @@ __device__ __forceinline__ uint32_t lerp_v2(uint32_t a, uint32_t b, uint32_t p)
 __device__ __forceinline__ uint32_t lerp_h(uint32_t a, uint32_t b, uint32_t f) { return lerp_h2(a, b, f); }
 __device__ __forceinline__ uint32_t lerp_v(uint32_t a, uint32_t b, uint32_t p) { return lerp_v2(a, b, p); }
 
+// One source pixel as the scaler sees it.  While the picture does not grow the scaler runs in front of the
+// matrix, on the raw B,G,R,X bytes; when it grows (g.scale_after) upstream scales behind the matrix, so each
+// source pixel is converted first and the 2-tap blends run on its Y,U,V bytes.
+__device__ __forceinline__ uint32_t to_yuv_word(uint32_t px, const SkGeom &g)
+{
+    const uint32_t ay = dp4a_uu(px, g.cy, g.y_off);
+    const uint32_t au = dp4a_us(px, g.cu, (int)g.c_off);
+    const uint32_t av = dp4a_us(px, g.cv, (int)g.c_off);
+    return __byte_perm(__byte_perm(ay, au, 0x0051), av, 0x7510);      // Y | U<<8 | V<<16 (sums < 65536)
+}
+__device__ __forceinline__ uint32_t source_px(const uint8_t *p, const SkGeom &g)
+{
+    const uint32_t v = ld4<0>(p);
+    return g.scale_after ? to_yuv_word(v, g) : v;
+}
+
 __device__ __forceinline__ uint32_t sample_px(const uint8_t *in, const SkGeom &g, int x, int o, int o2, uint32_t p)
 {
     int x0 = x;
@@ -621,17 +637,30 @@ __device__ __forceinline__ uint32_t sample_px(const uint8_t *in, const SkGeom &g
     }
     const uint8_t *r0 = in + (size_t)o * g.in_stride + 4 * (size_t)x0;
     const uint8_t *r1 = in + (size_t)o2 * g.in_stride + 4 * (size_t)x0;
-    uint32_t a0 = ld4<0>(r0);
-    uint32_t b0 = g.scale_v ? ld4<0>(r1) : 0;
+    uint32_t a0 = source_px(r0, g);
+    uint32_t b0 = g.scale_v ? source_px(r1, g) : 0;
     if (!g.scale_h)
         return g.scale_v ? lerp_v(a0, b0, p) : a0;
-    uint32_t a1 = ld4<0>(r0 + 4);
-    uint32_t b1 = g.scale_v ? ld4<0>(r1 + 4) : 0;
+    // (SK_PS_HINC_PLAIN can put the last output pixel exactly on the last source pixel: its second tap has
+    //  weight 0 and must not be fetched from beyond the row)
+    const int next = (x0 + 1 < g.in_w) ? 4 : 0;
+    uint32_t a1 = source_px(r0 + next, g);
+    uint32_t b1 = g.scale_v ? source_px(r1 + next, g) : 0;
     if (!g.scale_v)
         return lerp_h(a0, a1, fr);
     if (g.h_first)
         return lerp_v(lerp_h(a0, a1, fr), lerp_h(b0, b1, fr), p);
     return lerp_h(lerp_v(a0, b0, p), lerp_v(a1, b1, p), fr);
+}
+
+// Four already converted pixels (Y | U<<8 | V<<16) -> packed Y word and the four (U | V<<16) pairs.
+__device__ __forceinline__ void split_yuv_quad(const uint4 &q, uint32_t &yw, uint32_t uv[4])
+{
+    yw = __byte_perm(__byte_perm(q.x, q.y, 0x0040), __byte_perm(q.z, q.w, 0x0040), 0x5410);
+    uv[0] = __byte_perm(q.x, 0u, 0x4241);
+    uv[1] = __byte_perm(q.y, 0u, 0x4241);
+    uv[2] = __byte_perm(q.z, 0u, 0x4241);
+    uv[3] = __byte_perm(q.w, 0u, 0x4241);
 }
 
 // SW = true: the parity-switch instantiation (g.switches, g.y_off / g.c_off honoured); SW = false: the
@@ -676,16 +705,21 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
             q.w = sample_px(f.in, g, x + 3, o, o2, p);
         }
         uint32_t yw, uv[4];
-        if (SW) matrix_quad_sw(q, g, yw, uv);
+        if (g.scale_after) split_yuv_quad(q, yw, uv);
+        else if (SW) matrix_quad_sw(q, g, yw, uv);
         else matrix_quad(q, g, yw, uv);
         uint32_t left = 0;
         if (SITE == 1) {
             left = __shfl_up_sync(kFull, uv[3], 1);
             if (lane == 0) {
                 uint32_t hp = (bx0 > 0 && rows_valid) ? sample_px(f.in, g, bx0 - 1, o, o2, p) : 0;
-                uint32_t au = dp4a_us(hp, g.cu, SW ? (int)g.c_off : 32768);
-                uint32_t av = dp4a_us(hp, g.cv, SW ? (int)g.c_off : 32768);
-                left = __byte_perm(au, av, 0x7531);
+                if (g.scale_after) {
+                    left = __byte_perm(hp, 0u, 0x4241);
+                } else {
+                    uint32_t au = dp4a_us(hp, g.cu, SW ? (int)g.c_off : 32768);
+                    uint32_t av = dp4a_us(hp, g.cv, SW ? (int)g.c_off : 32768);
+                    left = __byte_perm(au, av, 0x7531);
+                }
             }
         }
         if (SW) {

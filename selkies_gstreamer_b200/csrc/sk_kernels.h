@@ -28,6 +28,7 @@ struct SkGeom {
     int32_t h_inc;            // 16.16 edge-aligned increment
     int h_first;              // order of the two 2-tap passes
     int scale_h, scale_v;     // which axes actually change size
+    int scale_after;          // 1: the picture grows, the scaler runs behind the matrix (generic kernel only)
     int scale_fast;           // 1: the shared-memory tiled kernel applies (set by the session runtime)
     int scale_tile_rows;      // tiled kernel: output rows per CTA tile, 16 or 32
     int scale_inplace;        // tiled kernel: h-scaled rows overwrite their raw rows (no second shared buffer)

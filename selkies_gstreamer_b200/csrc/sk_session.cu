@@ -204,10 +204,6 @@ int validate(const sk_config &c, std::string &why)
     if (scaling) {
         if (c.scale_method != SK_SCALE_BILINEAR) { why = "only scale_method bilinear is supported"; return SK_ERR_UNSUPPORTED; }
         if (c.scale_variant != SK_SCALE_VARIANT_GST_LQ && c.scale_variant != SK_SCALE_VARIANT_PLAIN_LQ) { why = "unknown scale_variant"; return SK_ERR_ARG; }
-        if ((int64_t)c.out_width * c.out_height > (int64_t)c.in_width * c.in_height) {
-            why = "enlarging (more output than input pixels) is not supported";
-            return SK_ERR_UNSUPPORTED;
-        }
     }
     return SK_OK;
 }
@@ -714,7 +710,8 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         g.scale_tile_rows = tile32 ? 32 : 16;
         g.scale_rows = max_rows;
         const size_t smem = (size_t)max_rows * row_words * 4;
-        g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
+        // (a growing picture is scaled behind the matrix: generic kernel)
+        g.scale_fast = (order_ok && !g.scale_after && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
                         (tile32 || max_rows <= 40) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
         // how far ahead a CTA asks for a window to be brought into L2: the CTAs resident on this GPU

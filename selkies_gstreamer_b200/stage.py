@@ -317,8 +317,8 @@ class PreEncodeStage:
     def transform_caps(self, direction: str, caps: list[dict], filter_caps: list[dict] | None = None) -> list[dict]:
         """Caps possible on the OTHER pad given `caps` on the `direction` pad.
 
-        Format becomes every format of the other side, size becomes the range this
-        stage can produce/accept (it shrinks, never enlarges), colorimetry and
+        Format becomes every format of the other side, size becomes the full range
+        (the stage scales both ways; fixate_caps prefers the input size), colorimetry and
         chroma-site do not carry across an RGB↔YUV change; everything else
         (framerate, pixel-aspect-ratio, ...) is kept."""
         out = []
@@ -335,13 +335,7 @@ class PreEncodeStage:
                  if k not in ("format", "colorimetry", "chroma-site", "width", "height", "features")}
             o["format"] = other_formats
             for dim in ("width", "height"):
-                v = st.get(dim, IntRange(MIN_DIM, MAX_DIM))
-                if isinstance(v, int):
-                    o[dim] = IntRange(MIN_DIM, v) if direction == SINK else IntRange(v, MAX_DIM)
-                elif isinstance(v, IntRange):
-                    o[dim] = IntRange(MIN_DIM, v[1]) if direction == SINK else IntRange(v[0], MAX_DIM)
-                else:
-                    o[dim] = IntRange(MIN_DIM, MAX_DIM)
+                o[dim] = IntRange(MIN_DIM, MAX_DIM)       # like upstream videoconvertscale: any size either way
             out.append(o)
             if direction == SINK and cuda:
                 out.append(dict(o, features=CUDA_FEATURE))

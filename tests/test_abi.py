@@ -68,7 +68,7 @@ def test_bad_struct_size_is_rejected(lib):
     (dict(parity_switches=1 << 9), _abi.SK_ERR_ARG),                         # unknown switch bit
     (dict(flags=_abi.SK_FLAG_GATED_READBACK), _abi.SK_ERR_ARG),              # needs SK_FLAG_HOST_OUTPUT
     (dict(flags=_abi.SK_FLAG_GATED_READBACK | _abi.SK_FLAG_HOST_OUTPUT | _abi.SK_FLAG_NO_DAMAGE), _abi.SK_ERR_ARG),
-    (dict(out_width=3840, out_height=2160), _abi.SK_ERR_UNSUPPORTED),   # enlarging
+    (dict(out_width=1280, out_height=720, scale_method=2), _abi.SK_ERR_UNSUPPORTED),   # only bilinear
     (dict(damage_block_threshold=300), _abi.SK_ERR_ARG),
     (dict(paint_over_trigger_frames=-1), _abi.SK_ERR_ARG),
 ])

@@ -298,10 +298,60 @@ def test_config3_desktop_content_bt709():
     check_sequence([f0, f1, f1], 2560, 1440, out_w=1920, out_h=1080, out_format="I420", colorimetry="bt709")
 
 
-def test_enlarging_is_rejected():
-    with pytest.raises(PreencodeError) as e:
-        PreencodeSession(640, 360, out_width=1280, out_height=720)
-    assert e.value.code == _abi.SK_ERR_UNSUPPORTED
+# Enlarging (more output than input pixels): upstream scales behind the matrix, on the converted samples.
+@pytest.mark.parametrize("dims", [(32, 24, 64, 48), (64, 48, 98, 50), (30, 20, 32, 48), (64, 24, 20, 96),
+                                  (96, 20, 128, 18), (130, 66, 258, 130), (640, 360, 1280, 720)])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_enlarging_parity(dims, variant):
+    w, h, ow, oh = dims
+    assert ow * oh > w * h
+    f0 = rand_frame(w, h, w + oh + variant)
+    f1 = synth.mutate(f0, 0.05, seed=variant, aligned=False)
+    for out_format, site, col in (("I420", 1, 1), ("NV12", 0, 0), ("NV12", 1, 2)):
+        check_sequence([f0, f1, f1], w, h, out_w=ow, out_h=oh, variant=variant, out_format=out_format, chroma_site=site,
+                       colorimetry=col)
+
+
+def test_enlarging_1080p_to_4k_rgbx_desktop_content():
+    f0 = synth.desktop(1920, 1080)[..., [2, 1, 0, 3]].copy()
+    f1 = synth.mutate(f0, 0.01, seed=4, aligned=False)
+    check_sequence([f0, f1], 1920, 1080, out_w=3840, out_h=2160, out_format="NV12", in_format="RGBx")
+
+
+def test_enlarging_through_the_switch_kernel_and_in_a_batch():
+    """SK_PS_MATRIX_ROUND moves the matrix offsets: behind-the-matrix scaling must honour it per source pixel;
+    and three sessions of one launch must each get their own frame."""
+    from oracle import cpu_oracle as oo
+    w, h, ow, oh = 96, 54, 160, 90
+    f = rand_frame(w, h, 77)
+    with PreencodeSession(w, h, out_width=ow, out_height=oh, out_format="I420", colorimetry=1, chroma_site=1,
+                          parity_switches=oo.PS_MATRIX_ROUND) as s:
+        exp = o.convert(f, ow, oh, out_fmt=1, matrix=1, chroma_site=1, switches=oo.PS_MATRIX_ROUND)
+        assert (s.convert(f).frame == exp).all()
+    frames = [rand_frame(w, h, 100 + i) for i in range(3)]
+    nexts = [synth.mutate(fr, 0.1, seed=i, aligned=False) for i, fr in enumerate(frames)]
+    sess = [PreencodeSession(w, h, out_width=ow, out_height=oh, colorimetry=1, chroma_site=1) for _ in frames]
+    try:
+        for s_, fr, nx in zip(sess, frames, nexts):          # a first pass each brings both inputs into HBM
+            s_.upload(0, fr); s_.wait(s_.submit(0))
+            s_.upload(1, nx); s_.wait(s_.submit(1))
+            s_.reset_history()
+        b = SessionBatch(sess)
+        stride = sess[0].device_input(0)[1]
+        prev = [None] * len(sess)
+        for fid, (slot, ins) in enumerate(((0, frames), (1, nexts))):
+            b.submit(b.frame_set([s_.device_input(slot)[0] for s_ in sess]), stride, 10 + fid)
+            b.wait(10 + fid)
+            for i, (s_, fr) in enumerate(zip(sess, ins)):
+                r = s_.wait(10 + fid)
+                exp = o.convert(fr, ow, oh, matrix=1, chroma_site=1)
+                assert (r.frame == exp).all()
+                em, en = o.damage(ow, oh, 0, exp, prev[i])
+                assert (r.damage_map == em).all() and r.damaged_count == en
+                prev[i] = exp
+    finally:
+        for s_ in sess:
+            s_.close()
 
 
 # ---- device-resident and batched submission -------------------------------------

@@ -192,9 +192,48 @@ def test_scale_flat_colour_is_preserved():
         assert (y == ey).all() and (u == eu).all() and (v == ev).all()
 
 
-def test_enlarging_is_rejected():
-    with pytest.raises(ValueError):
-        o.convert(np.zeros((16, 16, 4), np.uint8), 32, 32)
+# Enlarging: upstream's chain_scale() runs behind the matrix (on AYUV) once the picture grows.
+ENLARGE_DIMS = [(32, 24, 64, 48), (64, 48, 98, 50), (30, 20, 32, 48), (64, 24, 20, 96), (96, 20, 128, 18),
+                (1280, 720, 1920, 1080)]
+
+
+@pytest.mark.parametrize("dims", ENLARGE_DIMS)
+def test_enlarging_c_oracle_equals_numpy_restatement(dims):
+    w, h, ow, oh = dims
+    assert ow * oh > w * h
+    f = np.random.default_rng(w + oh).integers(0, 256, (h, w, 4), dtype=np.uint8)
+    for var in (o.SCALE_GST_LQ, o.SCALE_PLAIN_LQ):
+        off, tap = o.resampler_2tap(h, oh, var)
+        for fmt, site, sname in ((o.OUT_I420, o.SITE_H_COSITED, "h-cosited"), (o.OUT_NV12, o.SITE_NONE, "none")):
+            out = o.convert(f, ow, oh, scale_variant=var, n_threads=3, out_fmt=fmt, chroma_site=site)
+            y, u, v = o.split_planes(out, ow, oh, fmt)
+            Y, U, V = npr.convert(f, out_w=ow, out_h=oh, v_off=off, v_tap=tap, h_inc=o.h_increment(w, ow), site=sname)
+            assert (y == Y).all() and (u == U).all() and (v == V).all()
+
+
+def test_enlarging_flat_colour_is_preserved_and_threads_do_not_matter():
+    for vec in KAT["vectors"]:
+        out = o.convert(flat(vec["rgb"], 32, 24), 80, 50, matrix=o.MATRIX_BT709)
+        y, u, v = o.split_planes(out, 80, 50, o.OUT_NV12)
+        ey, eu, ev = vec["yuv"][1]
+        assert (y == ey).all() and (u == eu).all() and (v == ev).all()
+    f = np.random.default_rng(5).integers(0, 256, (36, 50, 4), dtype=np.uint8)
+    assert (o.convert(f, 100, 72, n_threads=1) == o.convert(f, 100, 72, n_threads=5)).all()
+
+
+def test_enlarging_scales_converted_samples_not_rgb():
+    """The two orders differ: a red/blue edge blended in RGB and then converted is not the blend of the two
+    converted colours once the matrix rows have been floored separately."""
+    f = np.zeros((8, 8, 4), np.uint8)
+    f[:, :4] = (0, 0, 255, 255)        # BGRx red
+    f[:, 4:] = (255, 0, 0, 255)        # BGRx blue
+    off, tap = o.resampler_2tap(8, 16)
+    Y, U, V = npr.convert(f, out_w=16, out_h=16, v_off=off, v_tap=tap, h_inc=o.h_increment(8, 16))
+    out = o.convert(f, 16, 16)
+    y, u, v = o.split_planes(out, 16, 16, o.OUT_NV12)
+    assert (y == Y).all() and (u == U).all() and (v == V).all()
+    yl, yr = int(y[0, 0]), int(y[0, -1])
+    assert all(min(yl, yr) <= int(t) <= max(yl, yr) for t in y[0])       # a blend of the two converted lumas
 
 
 # ---- damage ----------------------------------------------------------------

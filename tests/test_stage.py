@@ -75,7 +75,7 @@ def test_transform_caps_sink_to_src():
     assert len(out) == 1
     o = out[0]
     assert o["format"] == ["NV12", "I420"]
-    assert o["width"] == IntRange(2, 2560) and o["height"] == IntRange(2, 1440)     # shrink only
+    assert o["width"] == IntRange(2, 8192) and o["height"] == IntRange(2, 8192)     # scales both ways
     assert o["framerate"] == Fraction(60, 1)
     assert "colorimetry" not in o
     # the downstream capsfilter (gstwebrtc_app.py:614-617) forces the format
@@ -89,7 +89,7 @@ def test_transform_caps_src_to_sink_and_rejects_other_memory():
     src = st.parse_caps("video/x-raw, format=(string)I420, width=(int)1920, height=(int)1080")
     out = s.transform_caps(st.SRC, src)
     assert out[0]["format"] == list(st.SINK_FORMATS)
-    assert out[0]["width"] == IntRange(1920, 8192)
+    assert out[0]["width"] == IntRange(2, 8192)
     assert s.transform_caps(st.SINK, st.parse_caps("video/x-raw(memory:GLMemory), format=(string)BGRx")) == []
     assert s.transform_caps(st.SINK, st.parse_caps("audio/x-raw, format=(string)S16LE")) == []
 

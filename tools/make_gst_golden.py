@@ -76,7 +76,9 @@ def cases():
     out.append(("edge_1920x1080_rgbx", synth.desktop(1920, 1080)[..., [2, 1, 0, 3]].copy(), "rgbx", 1920, 1080, "NV12",
                 "bt709", "mpeg2", CONVERT))
     # scaling (BASELINE.json config 3 and small ragged ones), one converter and two converters
-    for (w, h, ow, oh) in ((2560, 1440, 1920, 1080), (64, 48, 32, 24), (100, 60, 98, 34), (64, 48, 64, 24), (64, 48, 30, 48)):
+    # ... and enlarging ones (more output than input pixels: upstream then scales behind the matrix)
+    for (w, h, ow, oh) in ((2560, 1440, 1920, 1080), (64, 48, 32, 24), (100, 60, 98, 34), (64, 48, 64, 24), (64, 48, 30, 48),
+                           (1280, 720, 1920, 1080), (32, 24, 64, 48), (64, 24, 20, 96), (96, 20, 128, 18)):
         f = synth.noise(w, h, seed=w + oh)
         for stage in (CONVERTSCALE, CONVERT_THEN_SCALE):
             tag = "one" if stage is CONVERTSCALE else "two"
