@@ -932,6 +932,38 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             }
         }
     }
+    // Pass A's per-thread set-up does not need the window: it runs while the copy is in flight.
+    // Column k of this lane is output pixel bx0 + lane + 32k: byte offset of its first source pixel inside a
+    // raw row, and the dp2a weight pair of its two horizontal taps.
+    uint32_t rel4[4], fr[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int xo = bx0 + lane + 32 * k;
+        const int xc = (FULL || xo < w) ? xo : xo_last;
+        rel4[k] = 4u * (uint32_t)(xc - cx0);
+        fr[k] = 0;
+        if (SH) {
+            const int32_t acc = xc * g.h_inc;
+            rel4[k] = 4u * (uint32_t)((acc >> 16) - cx0);
+            const uint32_t fq = (uint32_t)(acc >> 8) & 0xffu;
+            fr[k] = (256u - fq) | (fq << 16);          // the dp2a weight pair, built once per column
+        }
+    }
+    // Shared-space addresses by hand, one register per column (and one for the stores) that already holds
+    // this warp's first row; the empty asm keeps the compiler from re-deriving them row by row.  With a
+    // compile-time stride (RS) every further row is an immediate offset, otherwise one add per register.
+    const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + (uint32_t)warp * RSB;
+    uint32_t ak[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        ak[k] = raw_s + rel4[k];
+        asm volatile("" : "+r"(ak[k]));
+    }
+    uint32_t os = (uint32_t)__cvta_generic_to_shared(Sb) + 4u * (uint32_t)(lane + warp * Ss);
+    asm volatile("" : "+r"(os));
+#pragma unroll
+    for (int k = 0; k < 4; k++) asm volatile("" : "+r"(fr[k]));
+
     // One warp polls the mbarrier; the other seven sleep at the CTA barrier instead of spending issue
     // slots on try_wait loops (this kernel is issue-bound, not HBM-bound).
     if (warp == 0) mbar_wait(bar, 0);
@@ -940,20 +972,6 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     // ---- pass A: h-scale (or copy) the window once into the second shared buffer; lanes own
     //      adjacent output columns, so the gathers are (nearly) bank-conflict free
     {
-        uint32_t rel4[4], fr[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int xo = bx0 + lane + 32 * k;
-            const int xc = (FULL || xo < w) ? xo : xo_last;
-            rel4[k] = 4u * (uint32_t)(xc - cx0);
-            fr[k] = 0;
-            if (SH) {
-                const int32_t acc = xc * g.h_inc;
-                rel4[k] = 4u * (uint32_t)((acc >> 16) - cx0);
-                const uint32_t fq = (uint32_t)(acc >> 8) & 0xffu;
-                fr[k] = (256u - fq) | (fq << 16);          // the dp2a weight pair, built once per column
-            }
-        }
         const uint8_t *rawb = reinterpret_cast<const uint8_t *>(RAW);
         // The halo column (output pixel bx0-1, needed by the cosited chroma filter of the tile's first
         // quad): ONE warp h-scales it for every window row, lane = row, instead of every warp spending
@@ -981,18 +999,6 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 HALO[48 + lane] = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
             }
         }
-        // Shared-space addresses by hand, one register per column (and one for the stores) that already holds
-        // this warp's first row; the empty asm keeps the compiler from re-deriving them row by row.  With a
-        // compile-time stride (RS) every further row is an immediate offset, otherwise one add per register.
-        const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(RAW) + (uint32_t)warp * RSB;
-        uint32_t ak[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            ak[k] = raw_s + rel4[k];
-            asm volatile("" : "+r"(ak[k]));
-        }
-        uint32_t os = (uint32_t)__cvta_generic_to_shared(Sb) + 4u * (uint32_t)(lane + warp * Ss);
-        asm volatile("" : "+r"(os));
 #pragma unroll
         for (int i = 0; i < RPW; i++) {
             const uint32_t ioff = RS ? (uint32_t)i * 8u * 4u * (uint32_t)RS : 0u;      // same stride for loads and stores
