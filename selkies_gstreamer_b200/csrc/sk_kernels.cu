@@ -832,7 +832,9 @@ __device__ __forceinline__ uint32_t batch_vpack(const SkFrame &f, int y) { retur
 // RS = words per staged raw row when the session rounded the window width up to one of the compiled classes
 // (in-place layout only), 0 = taken from the geometry at run time.  A compile-time row stride turns every
 // row step of pass A into an immediate offset of the LDS / STS instructions.
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool FULL>
+// AFTER = the picture grows: the window's pixels are converted as they are picked up in pass A, both 2-tap
+// passes then blend Y,U,V bytes and pass B only has to split them (upstream scales behind the matrix then).
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool AFTER, bool FULL>
 __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, uint32_t *Sb, const int Ss_rt, uint32_t *RAW, uint32_t *HALO,
                                            const int bx0, const int by0, const int lane, const int warp,
                                            const int sy0, const int sy1,
@@ -986,8 +988,10 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
 #pragma unroll 1
             for (int r = lane; r < nr; r += 32) {
                 const uint8_t *R = rawb + (uint32_t)r * RSB;
-                const uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
-                HALO[r] = SH ? lerp_h2(ha, *reinterpret_cast<const uint32_t *>(R + hrel4 + 4), hf) : ha;
+                uint32_t ha = *reinterpret_cast<const uint32_t *>(R + hrel4);
+                uint32_t hb = SH ? *reinterpret_cast<const uint32_t *>(R + hrel4 + 4) : 0u;
+                if (AFTER) { ha = to_yuv_word(ha, g);  hb = SH ? to_yuv_word(hb, g) : 0u; }
+                HALO[r] = SH ? lerp_h2(ha, hb, hf) : ha;
             }
             __syncwarp();
             // ... and finishes it: lane = output row of the tile, vertical 2-tap + the two chroma dot
@@ -996,7 +1000,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 const int ra = SV ? (int)hvp.x - sy0 : min(lane, nr - 1);
                 uint32_t hp = HALO[ra];
                 if (SV) hp = blend2(hp, HALO[ra + 1], hvp.y, 128u);
-                HALO[48 + lane] = __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
+                HALO[48 + lane] = AFTER ? __byte_perm(hp, 0u, 0x4241)
+                                        : __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
             }
         }
 #pragma unroll
@@ -1008,6 +1013,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 for (int k = 0; k < 4; k++) {
                     a[k] = lds32(ak[k] + ioff);
                     b[k] = SH ? lds32(ak[k] + ioff + 4u) : 0u;
+                    if (AFTER) { a[k] = to_yuv_word(a[k], g);  b[k] = SH ? to_yuv_word(b[k], g) : 0u; }
                 }
                 // in-place mode: the row's results overwrite the raw row they were read from, so every
                 // lane's reads of this row must precede any lane's writes
@@ -1052,7 +1058,8 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 }
             }
             uint32_t yw, uv[4];
-            matrix_quad(q, g, yw, uv);
+            if (AFTER) split_yuv_quad(q, yw, uv);
+            else matrix_quad(q, g, yw, uv);
             uint32_t left = 0;
             if (SITE == 1) {
                 left = __shfl_up_sync(kFull, uv[3], 1);
@@ -1086,7 +1093,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
 }
 
 // RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 6: <= 48); TR = output rows per tile.
-template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS>
+template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool AFTER>
 #ifndef SK_SCALE_CTAS32
 #define SK_SCALE_CTAS32 5
 #endif
@@ -1135,8 +1142,8 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     int nvx = 0;
     bool rows_valid[NG];
     const CUtensorMap *tmap = &maps.m[blockIdx.z];
-    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
-    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
+    if (full) scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, AFTER, true>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
+    else      scale_tile<FMT, SITE, DAMAGE, SH, SV, RPW, TR, RS, AFTER, false>(g, f, Sb, Ss, RAW, s_halo, bx0, by0, lane, warp, sy0, sy1, have_prev, diff, nvx, rows_valid, bar, tmap);
 
     if (DAMAGE) {
         __shared__ uint32_t s_mask[NG][8];
@@ -1324,9 +1331,9 @@ static cudaError_t tiled_dispatch(const SkGeom &g, const SkBatch *b, const SkTma
     dim3 grid((g.out_w + 127) / 128, (g.out_h + tr - 1) / tr, n);
     dim3 block(kThreads);
     const size_t smem = (size_t)g.scale_rows * ((g.scale_inplace ? 0 : kScaleRowWords) + (size_t)g.scale_raw_stride) * sizeof(uint32_t);
-#define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR, RS)                                          \
+#define SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, RPW, TR, RS, AFTER)                                   \
         {                                                                                             \
-            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR, RS>;                   \
+            auto kern = sk_scale_tiled_kernel<FMT, SITE, DMG, SH, SV, RPW, TR, RS, AFTER>;            \
             if (smem > 48 * 1024)                                                                     \
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
             if (resident) return cudaOccupancyMaxActiveBlocksPerMultiprocessor(resident, kern, kThreads, smem); \
@@ -1337,12 +1344,20 @@ static cudaError_t tiled_dispatch(const SkGeom &g, const SkBatch *b, const SkTma
 #define SK_TILED(FMT, SITE, DMG, SH, SV)                                                              \
     if (g.out_fmt == FMT && g.site == SITE && (g.damage != 0) == DMG && (g.scale_h != 0) == SH &&     \
         (g.scale_v != 0) == SV) {                                                                     \
-        if (tr == 32 && SH && rs == kScaleStride32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, (SH ? kScaleStride32 : 0)) \
-        else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0)                          \
-        else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0)                \
-        else if (SH && rs == kScaleStride16) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (SH ? kScaleStride16 : 0)) \
-        else if (SH && rs == kScaleStride16n) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (SH ? kScaleStride16n : 0)) \
-        else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, 0)                                        \
+        /* Specialised instantiations exist for the usual case only, both axes scaled (BOTH): the     \
+           compile-time row strides, and the growing picture (AFTER; 32-row tiles, or 16-row tiles    \
+           of <= 24 window rows - the session runtime sends everything else to the generic kernel). */ \
+        constexpr bool BOTH = SH && SV;                                                               \
+        if (BOTH && g.scale_after) {                                                                  \
+            if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0, BOTH)                     \
+            else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0, BOTH)                              \
+        }                                                                                             \
+        else if (tr == 32 && BOTH && rs == kScaleStride32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, (BOTH ? kScaleStride32 : 0), false) \
+        else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0, false)                   \
+        else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0, false)         \
+        else if (BOTH && rs == kScaleStride16) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (BOTH ? kScaleStride16 : 0), false) \
+        else if (BOTH && rs == kScaleStride16n) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (BOTH ? kScaleStride16n : 0), false) \
+        else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, 0, false)                                 \
         return cudaGetLastError();                                                                    \
     }
 #define SK_TILED_MODES(FMT, SITE, DMG) \

@@ -690,7 +690,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         // kScaleStride16) when they fit one: the TMA box simply reads a few columns more, and every row step
         // of the kernel becomes an immediate offset.
         auto stride_for = [&](bool t32, int rows) {
-            if (!g.scale_inplace) return need_stride;
+            if (!g.scale_inplace || !(g.scale_h && g.scale_v)) return need_stride;     // classes: both axes only
             if (t32) return need_stride <= kScaleStride32 ? kScaleStride32 : need_stride;
             if (rows <= 24) return need_stride;
             return need_stride <= kScaleStride16n ? kScaleStride16n : (need_stride <= kScaleStride16 ? kScaleStride16 : need_stride);
@@ -710,9 +710,11 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         g.scale_tile_rows = tile32 ? 32 : 16;
         g.scale_rows = max_rows;
         const size_t smem = (size_t)max_rows * row_words * 4;
-        // (a growing picture is scaled behind the matrix: generic kernel)
-        g.scale_fast = (order_ok && !g.scale_after && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
-                        (tile32 || max_rows <= 40) &&
+        // (a growing picture is scaled behind the matrix: the tiled kernel is compiled for that with 32-row
+        //  tiles and with 16-row tiles of up to 24 window rows only)
+        g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
+                        (tile32 || max_rows <= (g.scale_after ? 24 : 40)) &&
+                        (!g.scale_after || (g.scale_h && g.scale_v)) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
         // how far ahead a CTA asks for a window to be brought into L2: the CTAs resident on this GPU
         g.scale_prefetch = std::getenv("SELKIES_PREENCODE_SCALE_NO_PREFETCH") ? 0 : sk_scale_resident_ctas(g);

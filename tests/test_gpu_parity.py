@@ -302,14 +302,25 @@ def test_config3_desktop_content_bt709():
 @pytest.mark.parametrize("dims", [(32, 24, 64, 48), (64, 48, 98, 50), (30, 20, 32, 48), (64, 24, 20, 96),
                                   (96, 20, 128, 18), (130, 66, 258, 130), (640, 360, 1280, 720)])
 @pytest.mark.parametrize("variant", [0, 1])
-def test_enlarging_parity(dims, variant):
+@pytest.mark.parametrize("kernel", ["tiled", "generic"])
+def test_enlarging_parity(dims, variant, kernel):
+    """tiled = whatever the session picks (the tiled kernel when both axes change and the window fits)."""
     w, h, ow, oh = dims
     assert ow * oh > w * h
     f0 = rand_frame(w, h, w + oh + variant)
     f1 = synth.mutate(f0, 0.05, seed=variant, aligned=False)
     for out_format, site, col in (("I420", 1, 1), ("NV12", 0, 0), ("NV12", 1, 2)):
         check_sequence([f0, f1, f1], w, h, out_w=ow, out_h=oh, variant=variant, out_format=out_format, chroma_site=site,
-                       colorimetry=col)
+                       colorimetry=col, scale_generic=(kernel == "generic"))
+
+
+@pytest.mark.parametrize("dims", [(1280, 720, 1920, 1080), (1366, 768, 1920, 1080), (258, 130, 386, 258), (640, 360, 642, 362)])
+def test_enlarging_ragged_edges_tiled(dims):
+    w, h, ow, oh = dims
+    f0 = rand_frame(w, h, w * 3 + oh)
+    f1 = synth.mutate(f0, 0.05, seed=2, aligned=False)
+    for out_format, site in (("NV12", 1), ("I420", 0)):
+        check_sequence([f0, f1, f1], w, h, out_w=ow, out_h=oh, out_format=out_format, chroma_site=site)
 
 
 def test_enlarging_1080p_to_4k_rgbx_desktop_content():

@@ -18,3 +18,8 @@ ncu --set full --clock-control none -k regex:sk_convert_kernel -s 8 -c 1 -o $O/$
 ncu --set full --clock-control none --import-source on -k regex:sk_scale_tiled -s 70 -c 1 -o $O/${R}_scale_full \
     python tools/run_config.py 2560 1440 1920 1080 I420 32 4 > $O/ncu_sc.log 2>&1
 ls -la $O/*.ncu-rep | tail -5
+# other scale geometries, device-resident (profiles/r2_scale_kernel.md, bottom table)
+for c in "2560 1440 1920 1080 NV12 32" "3840 2160 1920 1080 NV12 16" "3840 2160 2560 1440 NV12 16" "1920 1080 1280 720 NV12 32" \
+         "1920 1080 3840 2160 NV12 8" "1280 720 1920 1080 I420 16"; do
+    echo "$c: $(python tools/run_config.py $c 30)"
+done > $O/${R}_scale_geometries.txt 2>&1; cat $O/${R}_scale_geometries.txt
