@@ -761,6 +761,10 @@ def run_b200(args, rank, world, local_rank, dist):
         configs["1080p_i420_single_session"] = device_config(
             sk, "1080p I420 + damage, ONE session per launch", 1920, 1080, 1920, 1080, "I420", 1, csteps * 2, local_rank,
             peak, single=True)
+        # not a BASELINE.json config (the reference never enlarges): the scale-behind-the-matrix chain, for the record
+        configs["1080p_to_4k_nv12_enlarge"] = device_config(
+            sk, "1920x1080 -> 3840x2160 bilinear (picture grows: scaled behind the matrix) -> NV12 + damage", 1920, 1080,
+            W, H, "NV12", 8, max(30, csteps // 3), local_rank, peak)
 
     if rank != 0:
         return
