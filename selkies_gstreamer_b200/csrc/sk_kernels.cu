@@ -1097,7 +1097,10 @@ template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int
 #ifndef SK_SCALE_CTAS32
 #define SK_SCALE_CTAS32 5
 #endif
-__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? SK_SCALE_CTAS32 : 3))
+#ifndef SK_SCALE_CTAS16
+#define SK_SCALE_CTAS16 5
+#endif
+__global__ void __launch_bounds__(kThreads, RPW == 3 ? 6 : (TR == 32 ? SK_SCALE_CTAS32 : SK_SCALE_CTAS16))
 sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatch batch,
                       const __grid_constant__ SkTmaps maps)
 {
