@@ -1000,7 +1000,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
                 const int ra = SV ? (int)hvp.x - sy0 : min(lane, nr - 1);
                 uint32_t hp = HALO[ra];
                 if (SV) hp = blend2(hp, HALO[ra + 1], hvp.y, 128u);
-                HALO[48 + lane] = AFTER ? __byte_perm(hp, 0u, 0x4241)
+                HALO[kScaleMaxRows + lane] = AFTER ? __byte_perm(hp, 0u, 0x4241)
                                         : __byte_perm(dp4a_us(hp, g.cu, 32768), dp4a_us(hp, g.cv, 32768), 0x7531);
             }
         }
@@ -1063,7 +1063,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
             uint32_t left = 0;
             if (SITE == 1) {
                 left = __shfl_up_sync(kFull, uv[3], 1);
-                if (lane == 0) left = HALO[48 + 16 * gi + 2 * warp + rr];     // unused when bx0 == 0
+                if (lane == 0) left = HALO[kScaleMaxRows + 16 * gi + 2 * warp + rr];     // unused when bx0 == 0
             }
             chroma_h<SITE>(uv, left, x, w, hh[rr][0], hh[rr][1]);
             uint8_t *oy = f.out + y_off + (uint32_t)rr * (uint32_t)g.y_stride;
@@ -1092,7 +1092,7 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     }
 }
 
-// RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 6: <= 48); TR = output rows per tile.
+// RPW = window rows per warp (3: window <= 24 rows, 5: <= 40, 7: <= 56 = kScaleMaxRows); TR = output rows per tile.
 template <int FMT, int SITE, bool DAMAGE, bool SH, bool SV, int RPW, int TR, int RS, bool AFTER>
 #ifndef SK_SCALE_CTAS32
 #define SK_SCALE_CTAS32 5
@@ -1114,7 +1114,7 @@ sk_scale_tiled_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ 
     uint32_t *Sb = (RS || g.scale_inplace) ? RAW + 8 : sk_smem + (size_t)g.scale_rows * g.scale_raw_stride;
     const int Ss = g.scale_inplace ? g.scale_raw_stride : kScaleRowWords;
     // h-scaled halo column (output pixel bx0-1), one entry per window row; then its chroma pair per output row
-    __shared__ uint32_t s_halo[48 + 32];
+    __shared__ uint32_t s_halo[kScaleMaxRows + 32];
     const SkFrame &f = batch.f[blockIdx.z];
     const int lane = threadIdx.x & 31;
     // the shuffle tells the compiler that the warp index is warp-uniform: row addressing and the row-count
@@ -1352,11 +1352,12 @@ static cudaError_t tiled_dispatch(const SkGeom &g, const SkBatch *b, const SkTma
            of <= 24 window rows - the session runtime sends everything else to the generic kernel). */ \
         constexpr bool BOTH = SH && SV;                                                               \
         if (BOTH && g.scale_after) {                                                                  \
-            if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0, BOTH)                     \
+            if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 7, 32, 0, BOTH)                     \
             else SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0, BOTH)                              \
         }                                                                                             \
-        else if (tr == 32 && BOTH && rs == kScaleStride32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, (BOTH ? kScaleStride32 : 0), false) \
-        else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 6, 32, 0, false)                   \
+        else if (tr == 32 && BOTH && rs == kScaleStride32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 7, 32, (BOTH ? kScaleStride32 : 0), false) \
+        else if (tr == 32 && BOTH && rs == kScaleStride16n) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 7, 32, (BOTH ? kScaleStride16n : 0), false) \
+        else if (tr == 32) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 7, 32, 0, false)                   \
         else if (g.scale_rows <= 24) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 3, 16, 0, false)         \
         else if (BOTH && rs == kScaleStride16) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (BOTH ? kScaleStride16 : 0), false) \
         else if (BOTH && rs == kScaleStride16n) SK_TILED_LAUNCH(FMT, SITE, DMG, SH, SV, 5, 16, (BOTH ? kScaleStride16n : 0), false) \

@@ -7,7 +7,8 @@
 
 constexpr int SK_MAX_BATCH = 32;
 // Row strides (words) the tiled scale kernel is also compiled for as constants: in-place windows of 32-row
-// tiles up to 192 words (shrink ratios up to ~1.4), of 16-row tiles up to 208 words (3:2) or 272 words (2:1).
+// tiles up to 192 words (shrink ratios up to ~1.4) or 208 words (3:2), of 16-row tiles 208 or 272 words (2:1).
+constexpr int kScaleMaxRows = 56;     // tallest staged window (8 warps x 7 rows)
 constexpr int kScaleStride32 = 192;
 constexpr int kScaleStride16n = 208;
 constexpr int kScaleStride16 = 272;

@@ -691,7 +691,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         // of the kernel becomes an immediate offset.
         auto stride_for = [&](bool t32, int rows) {
             if (!g.scale_inplace || !(g.scale_h && g.scale_v)) return need_stride;     // classes: both axes only
-            if (t32) return need_stride <= kScaleStride32 ? kScaleStride32 : need_stride;
+            if (t32) return need_stride <= kScaleStride32 ? kScaleStride32 : (need_stride <= kScaleStride16n ? kScaleStride16n : need_stride);
             if (rows <= 24) return need_stride;
             return need_stride <= kScaleStride16n ? kScaleStride16n : (need_stride <= kScaleStride16 ? kScaleStride16 : need_stride);
         };
@@ -699,10 +699,10 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         // SM; SELKIES_PREENCODE_SCALE_TILE=16|32 overrides the choice for A/B runs and tests.
         const size_t sep_words = g.scale_inplace ? 0 : 132;
         const size_t smem32 = (size_t)max_rows32 * (sep_words + (size_t)stride_for(true, max_rows32)) * 4;
-        bool tile32 = max_rows32 <= 48 && smem32 <= 56 * 1024 && g.out_h >= 64;
+        bool tile32 = max_rows32 <= kScaleMaxRows && smem32 <= 56 * 1024 && g.out_h >= 64;
         if (const char *e = std::getenv("SELKIES_PREENCODE_SCALE_TILE")) {
             if (std::atoi(e) == 16) tile32 = false;
-            else if (std::atoi(e) == 32) tile32 = max_rows32 <= 48 && smem32 <= 96 * 1024;
+            else if (std::atoi(e) == 32) tile32 = max_rows32 <= kScaleMaxRows && smem32 <= 96 * 1024;
         }
         if (tile32) max_rows = max_rows32;
         g.scale_raw_stride = stride_for(tile32, max_rows);
@@ -712,7 +712,7 @@ int sk_session_create(const sk_config *cfg_in, sk_session **out)
         const size_t smem = (size_t)max_rows * row_words * 4;
         // (a growing picture is scaled behind the matrix: the tiled kernel is compiled for that with 32-row
         //  tiles and with 16-row tiles of up to 24 window rows only)
-        g.scale_fast = (order_ok && max_rows <= 48 && max_chunks <= 96 && smem <= 96 * 1024 &&
+        g.scale_fast = (order_ok && max_rows <= kScaleMaxRows && max_chunks <= 96 && smem <= 96 * 1024 &&
                         (tile32 || max_rows <= (g.scale_after ? 24 : 40)) &&
                         (!g.scale_after || (g.scale_h && g.scale_v)) &&
                         !(c.flags & SK_FLAG_SCALE_GENERIC) && !s->generic_only) ? 1 : 0;
