@@ -33,6 +33,6 @@ src = open(os.path.join(ROOT, "selkies_gstreamer_b200", "csrc", "sk_kernels.cu")
 j = {"dram_bytes_per_frame": (rd + wr) / sessions, "kernel_sha": hashlib.sha256(src).hexdigest()[:16],
      "kernel": vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "sk_convert_kernel",
      "sessions_per_launch": sessions, "dram_bytes_read": rd, "dram_bytes_write": wr,
-     "source": f"{rep} ({how})"}
+     "source": f"{os.path.relpath(os.path.abspath(rep), ROOT)} ({how})"}
 json.dump(j, open(os.path.join(ROOT, "profiles", "traffic.json"), "w"), indent=1)
 print(json.dumps(j))

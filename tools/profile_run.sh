@@ -15,6 +15,8 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
 ncu --set full --clock-control none --import-source on -k regex:sk_convert_kernel -s 72 -c 1 -o $O/${R}_convert_full $B > $O/ncu_f.log 2>&1
 ncu --set full --clock-control none -k regex:sk_convert_kernel -s 8 -c 1 -o $O/${R}_convert_single \
     python tools/run_config.py 3840 2160 3840 2160 NV12 1 4 > $O/ncu_s.log 2>&1
+# (what comes back from the box is capped at 64 MiB: the single-session report travels as its digest only)
+python tools/ncu_digest.py $O/${R}_convert_single.ncu-rep 3 > $O/${R}_convert_single_digest.txt 2>&1 && rm -f $O/${R}_convert_single.ncu-rep
 ncu --set full --clock-control none --import-source on -k regex:sk_scale_tiled -s 70 -c 1 -o $O/${R}_scale_full \
     python tools/run_config.py 2560 1440 1920 1080 I420 32 4 > $O/ncu_sc.log 2>&1
 ls -la $O/*.ncu-rep | tail -5
