@@ -136,8 +136,18 @@ def measured_peak():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def code_sha(path: str) -> str:
+    """sha of a CUDA/C++ source with comments and white space taken out: what the compiler sees, so that an
+    edited comment does not make a measurement look stale (tools/make_traffic.py stamps with the same function)."""
+    import re
+    src = open(path, "r", encoding="utf-8", errors="replace").read()
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    src = re.sub(r"//[^\n]*", " ", src)
+    return hashlib.sha256("".join(src.split()).encode()).hexdigest()[:16]
+
+
 def kernel_sha() -> str:
-    return hashlib.sha256(open(KERNEL_SOURCE, "rb").read()).hexdigest()[:16]
+    return code_sha(KERNEL_SOURCE)
 
 
 def recorded_traffic(S: int):

@@ -814,12 +814,14 @@ sk_scale_kernel(const __grid_constant__ SkGeom g, const __grid_constant__ SkBatc
 
 // ---- tiled scale kernel (fast path) -------------------------------------------------
 // Used when the horizontal pass comes first (or only one axis changes) and the source
-// rows of a 16-row output tile fit the shared-memory window.  Two passes per CTA tile of
-// 128 x 16 output pixels:
-//   A  every needed source row is h-scaled ONCE into shared memory; lanes own adjacent
-//      output columns, so a warp's gathers touch ~2 cache lines instead of ~6;
+// rows of an output tile fit the shared-memory window (kScaleMaxRows).  Per CTA tile of
+// 128 x 32 (or 128 x 16) output pixels:
+//   -  the raw source window arrives by ONE 2-D tensor-map copy (TMA); meanwhile the CTA asks for its
+//      successor's window to be brought into L2;
+//   A  every window row is h-scaled ONCE into shared memory (in place over the raw row when it is long
+//      enough); lanes own adjacent output columns, so the gathers are (nearly) bank-conflict free;
 //   B  each thread takes 4 adjacent output pixels x 2 rows with 128-bit LDS, applies the
-//      vertical 2-tap, then the same matrix / chroma / store / damage tail as above.
+//      vertical 2-tap, then the same matrix / chroma / store / damage tail as above (once per 16 rows).
 constexpr int kScaleRowWords = 132;     // 128 columns + halo column (index 128), 16-byte aligned rows
 
 // All frames of a launch share the geometry, hence the vertical table: any frame's copy serves.
@@ -845,7 +847,6 @@ __device__ __forceinline__ void scale_tile(const SkGeom &g, const SkFrame &f, ui
     constexpr int NG = TR / 16;          // 16-row groups (= macroblock rows) per tile
     const int w = g.out_w, h = g.out_h;
 
-    // source-row window of this tile
     // f.v_pack[y] = {first source row, dp2a weight pair of the two vertical taps}; the second row is always
     // first + 1 (vertical_taps clamps first to in_h - 2), and the table is padded to an even length.
     const uint2 *vp = f.v_pack;

@@ -7,7 +7,6 @@ Writes dram__bytes_read.sum + dram__bytes_write.sum of the captured launch, divi
 that launch, together with the sha of the kernel source the library was built from: bench.py reports
 the figure as `roofline.traffic` only while that sha still matches (a later kernel edit makes it stale)."""
 import csv
-import hashlib
 import io
 import json
 import os
@@ -29,8 +28,10 @@ def metric(name):
 
 
 rd, wr = metric("dram__bytes_read.sum"), metric("dram__bytes_write.sum")
-src = open(os.path.join(ROOT, "selkies_gstreamer_b200", "csrc", "sk_kernels.cu"), "rb").read()
-j = {"dram_bytes_per_frame": (rd + wr) / sessions, "kernel_sha": hashlib.sha256(src).hexdigest()[:16],
+sys.path.insert(0, ROOT)
+from bench import code_sha  # noqa: E402  (comments and white space do not count)
+j = {"dram_bytes_per_frame": (rd + wr) / sessions,
+     "kernel_sha": code_sha(os.path.join(ROOT, "selkies_gstreamer_b200", "csrc", "sk_kernels.cu")),
      "kernel": vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "sk_convert_kernel",
      "sessions_per_launch": sessions, "dram_bytes_read": rd, "dram_bytes_write": wr,
      "source": f"{os.path.relpath(os.path.abspath(rep), ROOT)} ({how})"}
