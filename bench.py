@@ -422,7 +422,7 @@ class StageRig:
     pageable host buffers — what E pipelines of one process look like to the stage (buffer pools of
     ximagesrc upstream and of the encoder downstream, gstwebrtc_app.py:210-255, :941-994)."""
 
-    def __init__(self, E, inputs, local_rank, pool=3, **props):
+    def __init__(self, E, inputs, local_rank, pool=3, w=W, h=H, **props):
         from selkies_gstreamer_b200.stage import PreEncodeStage
         self.E, self.pool = E, pool
         self.stages, self.inbufs, self.outbufs = [], [], []
@@ -431,8 +431,8 @@ class StageRig:
             st.set_property("cuda-device-id", local_rank)
             for k, v in props.items():
                 st.set_property(k, v)
-            inc = {"name": "video/x-raw", "format": "BGRx", "width": W, "height": H}
-            outc = {"name": "video/x-raw", "format": "NV12", "width": W, "height": H, "colorimetry": "bt709",
+            inc = {"name": "video/x-raw", "format": "BGRx", "width": w, "height": h}
+            outc = {"name": "video/x-raw", "format": "NV12", "width": w, "height": h, "colorimetry": "bt709",
                     "chroma-site": "mpeg2"}
             st.start()
             if not st.set_caps(inc, outc):
@@ -657,6 +657,26 @@ def run_b200(args, rank, world, local_rank, dist):
         t = timed_rig(rig, 2, psteps, dist)[0]
         side["unpinned_fps"] = E * psteps * world / t
         rig.close()
+
+        # the same call at the reference's own default desktop size (BASELINE.json config 1: 1920x1080), with the
+        # host cores' rate for that size beside it (bounded 3 s sample)
+        if world == 1:
+            w1, h1 = 1920, 1080
+            in1 = make_inputs(E, rank, w1, h1)
+            rig = StageRig(E, in1, local_rank, w=w1, h=h1)
+            s1 = esteps * 4
+            t = statistics.median(timed_rig(rig, 2 * rig.pool, s1, dist, reps=3))
+            rig.close()
+            threads = len(os.sched_getaffinity(0))
+            prevs = cpu_pass([p[0] for p in in1], [None] * E, threads, w1, h1)
+            n1, t0 = 0, time.perf_counter()
+            while time.perf_counter() - t0 < 3.0:
+                prevs = cpu_pass([p[(n1 + 1) & 1] for p in in1], prevs, threads, w1, h1)
+                n1 += 1
+            side["config1_1080p"] = {"fps": E * s1 / t, "h2d_gbs": E * s1 * 4 * w1 * h1 / t / 1e9, "stages": E,
+                                     "cpu_port_fps": n1 * E / (time.perf_counter() - t0), "cpu_cores": threads,
+                                     "what": "PreEncodeStage.transform on 1920x1080 BGRx -> NV12 frames, pageable pool buffers, "
+                                             "median of 3 regions; C oracle on all host cores beside it"}
 
         # C ABI only, pre-filled pinned staging (round 1's e2e figure), frame + map read back
         esess = [sk.PreencodeSession(W, H, out_format="NV12", colorimetry="bt709", chroma_site="mpeg2",
