@@ -348,3 +348,48 @@ def test_stage_with_cuda_memory_caps_keeps_the_frame_on_the_gpu():
         assert (dmap == em).all() and cnt == en, k
         prev = e
     assert s.stop()
+
+
+# ---- resources come back ---------------------------------------------------------------------------
+def test_sessions_give_their_device_memory_back():
+    """Create, use and destroy sessions of every flavour many times over: the GPU's free memory must return to
+    where it was (first cycle excluded: context, modules and the tensor-map encoder load lazily)."""
+    torch = pytest.importorskip("torch")
+
+    def cycle(seed):
+        rng = np.random.default_rng(seed)
+        flavours = [
+            dict(w=640, h=360, kw={}),
+            dict(w=1280, h=720, kw=dict(out_width=854, out_height=480, out_format="I420")),
+            dict(w=640, h=360, kw=dict(out_width=1280, out_height=720)),                       # growing picture
+            dict(w=1920, h=1080, kw=dict(gated_readback=True, n_inflight=3)),
+            dict(w=512, h=288, kw=dict(policy=True, out_format="I420")),
+            dict(w=800, h=600, kw=dict(host_output=False, scale_generic=True, out_width=400, out_height=300)),
+        ]
+        for fl in flavours:
+            f = rng.integers(0, 256, (fl["h"], fl["w"], 4), dtype=np.uint8)
+            with PreencodeSession(fl["w"], fl["h"], colorimetry=1, chroma_site=1, **fl["kw"]) as s:
+                r = s.convert(f)
+                assert r.damaged_count > 0
+        members = [PreencodeSession(640, 360, colorimetry=1, chroma_site=1) for _ in range(4)]
+        try:
+            b = SessionBatch(members)
+            b.prepare()
+            frames = [rng.integers(0, 256, (360, 640, 4), dtype=np.uint8) for _ in members]
+            outs = [np.empty(m.frame_bytes, np.uint8) for m in members]
+            b.submit_host([f.ctypes.data for f in frames], 4 * 640, [o_.ctypes.data for o_ in outs], 1)
+            b.wait(1)
+            for m in members:
+                m.wait(1)
+        finally:
+            for m in members:
+                m.close()
+
+    cycle(0)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(0)
+    for k in range(1, 13):
+        cycle(k)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info(0)
+    assert free0 - free1 < (4 << 20), f"{(free0 - free1) / 2**20:.1f} MiB of device memory did not come back"
