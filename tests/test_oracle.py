@@ -301,3 +301,35 @@ def test_opencv_sanity_within_two():
     y = o.split_planes(o.convert(f, matrix=o.MATRIX_BT601, chroma_site=o.SITE_NONE, out_fmt=o.OUT_I420), 32, 32, o.OUT_I420)[0]
     ref = cv2.cvtColor(f, cv2.COLOR_BGRA2YUV_I420)[:32, :32]
     assert np.abs(y.astype(int) - ref.astype(int)).max() <= 2
+
+
+# ---- an anchor outside this repository: the standards' own equations --------------------------------
+ITU = {o.MATRIX_BT601: (0.299, 0.114), o.MATRIX_BT709: (0.2126, 0.0722), o.MATRIX_BT2020: (0.2627, 0.0593)}
+
+
+@pytest.mark.parametrize("matrix", [o.MATRIX_BT601, o.MATRIX_BT709, o.MATRIX_BT2020])
+def test_matrix_stays_within_the_itu_equations(matrix):
+    """E'Y = Kr R + Kg G + Kb B, Cb = (B - Y) / (2 (1 - Kb)), Cr = (R - Y) / (2 (1 - Kr)), quantised to 16 + 219 Y and
+    128 + 224 C (BT.601-7 / BT.709-6 / BT.2020-2, 8 bit).  The integer chain (8 fractional bits per coefficient, sums
+    floored, each coefficient off by up to half of 1/256) stays within 2.5 code values below and 1 above the real
+    value, and on average half a code value low — a floor, not a round."""
+    kr, kb = ITU[matrix]
+    kg = 1.0 - kr - kb
+    rng = np.random.default_rng(matrix)
+    rgb = rng.integers(0, 256, (64, 64, 3)).astype(np.float64)
+    rgb[0, :8] = [(0, 0, 0), (255, 255, 255), (255, 0, 0), (0, 255, 0), (0, 0, 255), (255, 255, 0), (0, 255, 255), (255, 0, 255)]
+    f = np.empty((64, 64, 4), np.uint8)
+    f[..., 0], f[..., 1], f[..., 2], f[..., 3] = rgb[..., 2], rgb[..., 1], rgb[..., 0], 255
+    # 4:4:4 view of the oracle: every pixel doubled in both directions, so each chroma sample is one colour's
+    big = np.repeat(np.repeat(f, 2, axis=0), 2, axis=1)
+    out = o.convert(np.ascontiguousarray(big), matrix=matrix, chroma_site=o.SITE_NONE, out_fmt=o.OUT_I420)
+    y, u, v = o.split_planes(out, 128, 128, o.OUT_I420)
+    r, g, b = rgb[..., 0] / 255, rgb[..., 1] / 255, rgb[..., 2] / 255
+    ey = kr * r + kg * g + kb * b
+    exact = (16 + 219 * ey, 128 + 224 * (b - ey) / (2 * (1 - kb)), 128 + 224 * (r - ey) / (2 * (1 - kr)))
+    for got, want in zip((y[::2, ::2], u, v), exact):
+        d = got.astype(np.float64) - want
+        assert d.max() <= 1.0 and d.min() > -2.5, (d.min(), d.max())
+        # (BT.709's Cb row -26 -87 +112 sums to -1/256 after per-coefficient rounding: that plane sits a whole code
+        #  value low on average, white comes out as U = 127 — SURVEY A.2/A.7, risk R8)
+        assert -1.1 < d.mean() < -0.1, d.mean()
