@@ -509,6 +509,25 @@ def test_stage_transform_and_renegotiation():
     assert s.stop()
 
 
+def test_stage_scales_both_ways_when_the_downstream_caps_ask_for_it():
+    """A capsfilter behind the stage that fixes another size (videoconvertscale's job): smaller, then larger."""
+    from selkies_gstreamer_b200 import stage as st
+    f = synth.desktop(1280, 720)
+    sink = st.parse_caps("video/x-raw, format=(string)BGRx, width=(int)1280, height=(int)720, framerate=(fraction)60/1")
+    for ow, oh in ((854, 480), (1920, 1080)):
+        s = st.PreEncodeStage()
+        filt = st.parse_caps(f"video/x-raw, format=(string)NV12, width=(int){ow}, height=(int){oh}")
+        other = s.transform_caps(st.SINK, sink, filt)
+        fixed = s.fixate_caps(st.SINK, sink, other)
+        assert (fixed["width"], fixed["height"]) == (ow, oh)
+        assert s.start() and s.set_caps(sink[0], fixed), s.last_error
+        out, m, n = s.transform_array(f)
+        site = s.session.site
+        assert (out == o.convert(f, ow, oh, out_fmt=o.OUT_NV12, matrix=s.session.matrix, chroma_site=site)).all()
+        assert m.all() and n == m.size
+        assert s.stop()
+
+
 # ---- temporal damage policy (in-kernel counters) ------------------------------------
 @pytest.mark.parametrize("knobs", [(10, 20, 15), (2, 3, 4)])
 @pytest.mark.parametrize("mode", ["convert", "scale"])
