@@ -28,6 +28,10 @@ CASES = [
     (100, 60, 98, 34, 1, 0, 0, 0, 0, 8),
     (64, 48, 64, 24, 0, 0, 1, 1, 0, 9),
     (64, 48, 30, 48, 0, 1, 1, 1, 0, 10),
+    # growing pictures: scaled behind the matrix
+    (32, 24, 64, 48, 0, 1, 1, 1, 0, 11),
+    (30, 20, 32, 48, 1, 0, 0, 0, 1, 12),
+    (64, 24, 20, 96, 0, 0, 2, 1, 0, 13),
 ]
 
 
