@@ -54,6 +54,8 @@ def main():
                                      "! b200preencode ! video/x-raw,format=NV12 ! fakesink"),
         ("convert + shrink 1440p->1080p I420", "videotestsrc num-buffers=30 ! video/x-raw,format=BGRx,width=2560,height=1440 "
                                                "! b200preencode ! video/x-raw,format=I420,width=1920,height=1080 ! fakesink"),
+        ("convert + enlarge 720p->1080p NV12", "videotestsrc num-buffers=30 ! video/x-raw,format=BGRx,width=1280,height=720 "
+                                               "! b200preencode ! video/x-raw,format=NV12,width=1920,height=1080 ! fakesink"),
         ("properties the reference sets", "videotestsrc num-buffers=10 ! video/x-raw,format=BGRx,width=640,height=360 "
                                           "! b200preencode n-threads=4 qos=true cuda-device-id=0 ! video/x-raw,format=NV12 ! fakesink"),
         ("ROI metas reach x264enc", "videotestsrc num-buffers=30 ! video/x-raw,format=BGRx,width=1280,height=720 "
